@@ -1,0 +1,201 @@
+"""Training driver: per-rank run, train / eval loops, logging, checkpointing.
+
+Maps onto the reference as follows:
+
+=====================  ====================================================
+reference              here
+=====================  ====================================================
+``run``  train.py:79   :func:`run` — seeds, per-rank batch ``ceil(B/size)``,
+                       shards, loaders, model, optimizer, StepLR, epoch loop,
+                       final save
+``train`` train.py:42  :meth:`Trainer.train_epoch` — same step order; the only
+                       host sync is ``loss.item()`` on rank 0 every
+                       ``log_interval`` batches
+``test``  train.py:60  :meth:`Trainer.test_epoch` — loss-sum / correct-count
+                       accumulate on the device; one D2H per epoch instead of
+                       two per batch; normalised by the local shard length
+=====================  ====================================================
+
+Two steppers implement one interface (``train_step``, ``eval_batch``,
+``eval_result``): :class:`EagerStepper` (torch ops + autograd + bucketed
+``torch.distributed`` reduction — CPU/gloo plumbing path and NCCL baseline) and
+:class:`b200dp.models.fused.NativeStepper` (hand-written sm_100a kernels, fused
+P2P reduce+update, CUDA-graph step).
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from . import ckpt
+from .data.shard import shard_for_rank
+from .data.synthetic import (CIFAR_SPEC, MNIST_SPEC, PinnedRingLoader, SyntheticImages,
+                             normalise_reference)
+from .models.lenet import LeNet, LeNetConfig, loss_fn
+from .optim.flat import OptHyper, StepLR
+from .parallel.ddp import DataParallel
+from .parallel.launch import RankContext
+from .utils.logging import RankLogger, test_line, train_line
+
+
+class EagerStepper:
+    """torch-eager forward/backward under :class:`DataParallel`."""
+
+    name = "eager"
+
+    def __init__(self, ctx: RankContext, cfg: LeNetConfig, hyper: OptHyper, *, loss_mode: str = "ref",
+                 spec=MNIST_SPEC, bucket_bytes: int = -1, overlap: bool = True):
+        self.ctx, self.cfg, self.loss_mode, self.spec = ctx, cfg, loss_mode, spec
+        model = LeNet(cfg).to(ctx.device)
+        self.ddp = DataParallel(model, hyper, bucket_bytes=bucket_bytes, overlap=overlap, device=ctx.device)
+        self.model = self.ddp.module
+        self.optimizer = self.ddp.optimizer
+        self._eval = torch.zeros(2, dtype=torch.float64, device=ctx.device)
+
+    def _prep(self, x: torch.Tensor) -> torch.Tensor:
+        return normalise_reference(x, self.spec) if x.dtype == torch.uint8 else x
+
+    def _out(self, x):
+        return self.model(x) if self.loss_mode == "ref" else self.model.logits(x)
+
+    def train_step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        self.model.train()
+        self.ddp.zero_grad()
+        loss = loss_fn(self._out(self._prep(x)), y, self.loss_mode)
+        loss.backward()
+        self.ddp.step()
+        return loss.detach()
+
+    @torch.no_grad()
+    def eval_batch(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        self.model.eval()
+        out = self._out(self._prep(x))
+        self._eval[0] += loss_fn(out, y, self.loss_mode, reduction="sum").double()
+        self._eval[1] += out.argmax(dim=1).eq(y).sum().double()
+
+    def eval_result(self, reset: bool = True) -> Tuple[float, int]:
+        vals = self._eval.tolist()  # the one D2H of the epoch
+        if reset:
+            self._eval.zero_()
+        return float(vals[0]), int(vals[1])
+
+    def replica_divergence(self) -> float:
+        return self.ddp.replica_divergence()
+
+
+class Trainer:
+    """Epoch loops around a stepper (reference ``train`` / ``test``)."""
+
+    def __init__(self, ctx: RankContext, stepper, logger: RankLogger, *, log_interval: int = 15,
+                 dry_run: bool = False, global_eval: bool = False):
+        self.ctx, self.stepper, self.log = ctx, stepper, logger
+        self.log_interval, self.dry_run, self.global_eval = log_interval, dry_run, global_eval
+        self.global_step = 0
+
+    def train_epoch(self, loader, epoch: int) -> Optional[float]:
+        last = None
+        n_batches = len(loader)
+        for batch_idx, (data, target) in enumerate(loader):
+            loss = self.stepper.train_step(data, target)
+            self.global_step += 1
+            if batch_idx % self.log_interval == 0 and self.ctx.is_main:
+                last = float(loss.item())  # the only host sync on the step path (train.py:55)
+                self.log.print(train_line(epoch, batch_idx, len(data), len(loader.dataset), n_batches, last))
+                self.log.event(kind="train", epoch=epoch, step=self.global_step, batch_idx=batch_idx, loss=last)
+            if self.dry_run:
+                break
+        return last
+
+    def test_epoch(self, loader) -> Tuple[float, int, int]:
+        for data, target in loader:
+            self.stepper.eval_batch(data, target)
+        loss_sum, correct = self.stepper.eval_result()
+        n = len(loader.dataset)
+        if self.global_eval and self.ctx.world_size > 1:
+            t = torch.tensor([loss_sum, correct, n], dtype=torch.float64, device=self.ctx.device)
+            dist.all_reduce(t)
+            loss_sum, correct, n = float(t[0]), int(t[1]), int(t[2])
+        test_loss = loss_sum / n
+        if self.ctx.is_main:
+            self.log.print(test_line(self.ctx.local_rank if self.ctx.device.type == "cuda" else 0,
+                                     test_loss, correct, n))
+            self.log.event(kind="test", loss=test_loss, correct=correct, n=n)
+        return test_loss, correct, n
+
+
+def build_stepper(ctx: RankContext, args, cfg: LeNetConfig, hyper: OptHyper, spec, per_rank_batch: int):
+    backend = getattr(args, "backend", None)
+    use_native = ctx.device.type == "cuda" and not getattr(args, "eager", False) and backend in (None, "b200")
+    if use_native:
+        from .models.fused import NativeStepper
+        return NativeStepper(ctx, cfg, hyper, batch=per_rank_batch, loss_mode=args.loss, spec=spec,
+                             algo=getattr(args, "allreduce_algo", "auto"),
+                             graph=not getattr(args, "no_graph", False),
+                             overlap=not getattr(args, "no_overlap", False),
+                             dtype=getattr(args, "dtype", "bf16"))
+    return EagerStepper(ctx, cfg, hyper, loss_mode=args.loss, spec=spec,
+                        bucket_bytes=getattr(args, "bucket_bytes", -1),
+                        overlap=not getattr(args, "no_overlap", False))
+
+
+def make_hyper(args) -> OptHyper:
+    return OptHyper(kind=args.optimizer, lr=args.lr, momentum=getattr(args, "momentum", 0.9),
+                    weight_decay=getattr(args, "weight_decay", 0.0))
+
+
+def run(ctx: RankContext, args) -> dict:
+    """Per-rank entry (reference ``run(rank, size, args)``, train.py:79-108)."""
+    torch.manual_seed(args.seed)                      # train.py:80 — same seed on every rank
+    if ctx.device.type == "cuda":
+        torch.cuda.manual_seed(args.seed)             # train.py:81
+    per_rank_batch = math.ceil(args.batch_size / ctx.world_size)   # train.py:82
+
+    spec = MNIST_SPEC if args.dataset == "mnist" else CIFAR_SPEC
+    cfg = LeNetConfig(in_ch=spec.channels, width_mult=args.width_mult, in_hw=spec.height)
+    base_train = SyntheticImages(args.train_size, spec, seed=args.seed * 7919 + 1)
+    base_test = SyntheticImages(args.test_size, spec, seed=args.seed * 7919 + 2)
+    compat = getattr(args, "compat_shard", False)
+    tr = shard_for_rank(base_train, ctx.rank, ctx.world_size, compat=compat and ctx.world_size > 1)
+    te = shard_for_rank(base_test, ctx.rank, ctx.world_size, compat=compat and ctx.world_size > 1)
+
+    on_gpu = ctx.device.type == "cuda"
+    fmt = "u8" if on_gpu else "f32"
+    mk = lambda base, sh: PinnedRingLoader(  # noqa: E731  (train.py:95-96: both loaders shuffle)
+        base.images, base.targets, *sh.bounds(), per_rank_batch, spec, shuffle=True, fmt=fmt,
+        device=ctx.device if on_gpu else None, seed=args.seed + 17 * ctx.rank)
+    train_loader, test_loader = mk(base_train, tr), mk(base_test, te)
+
+    stepper = build_stepper(ctx, args, cfg, make_hyper(args), spec, per_rank_batch)
+    scheduler = StepLR(stepper.optimizer, step_size=1, gamma=args.gamma)     # train.py:101
+    logger = RankLogger(ctx.is_main, getattr(args, "jsonl", None))
+    trainer = Trainer(ctx, stepper, logger, log_interval=args.log_interval, dry_run=args.dry_run,
+                      global_eval=getattr(args, "global_eval", False))
+
+    start_epoch = 1
+    if getattr(args, "resume", None):
+        meta = ckpt.load_full(args.resume, model=stepper.model, optimizer=stepper.optimizer,
+                              scheduler=scheduler)
+        if hasattr(stepper, "params_changed"):
+            stepper.params_changed()
+        start_epoch = meta["epoch"] + 1
+        trainer.global_step = meta["step"]
+
+    result = {}
+    for epoch in range(start_epoch, args.epochs + 1):                         # train.py:102-105
+        last = trainer.train_epoch(train_loader, epoch)
+        test_loss, correct, n = trainer.test_epoch(test_loader)
+        scheduler.step()
+        result = {"epoch": epoch, "train_loss": last, "test_loss": test_loss, "correct": correct, "n": n}
+        if getattr(args, "save_full", None):
+            ckpt.save_full(args.save_full, model=stepper.model, optimizer=stepper.optimizer,
+                           scheduler=scheduler, epoch=epoch, step=trainer.global_step,
+                           is_main=ctx.is_main)
+
+    if args.save_model:                                                       # train.py:107-108
+        ckpt.save_model(stepper.model, getattr(args, "checkpoint", ckpt.DEFAULT_NAME), is_main=ctx.is_main)
+    result["divergence"] = stepper.replica_divergence() if ctx.world_size > 1 else 0.0
+    logger.close()
+    return result
