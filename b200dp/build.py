@@ -1,0 +1,84 @@
+"""Build the in-tree CUDA library (csrc/*.cu -> b200dp/_native/libb200dp.so) for sm_100a.
+
+nvcc cross-compiles without a GPU, so this runs on the CPU authoring box; the
+built .so travels to the B200 box with the repo snapshot.  Rebuilds only when a
+source is newer than the library.  ``python -m b200dp.build [--force]``.
+"""
+from __future__ import annotations
+
+import glob
+import os
+import shutil
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(ROOT, "csrc")
+OUT_DIR = os.path.join(ROOT, "b200dp", "_native")
+OBJ_DIR = os.path.join(OUT_DIR, "obj")
+LIB = os.path.join(OUT_DIR, "libb200dp.so")
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+NVCC_FLAGS = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "--use_fast_math=false",
+              "-Xptxas", "-v", "--expt-relaxed-constexpr"]
+
+
+def _nvcc() -> str:
+    exe = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(exe):
+        raise RuntimeError("nvcc not found")
+    return exe
+
+
+def sources():
+    return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
+
+
+def _deps_mtime() -> float:
+    files = sources() + glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(ROOT, "include", "*.h"))
+    return max(os.path.getmtime(f) for f in files)
+
+
+def needs_build() -> bool:
+    return not os.path.exists(LIB) or os.path.getmtime(LIB) < _deps_mtime()
+
+
+def _compile(src: str, log_dir: str) -> str:
+    obj = os.path.join(OBJ_DIR, os.path.basename(src)[:-3] + ".o")
+    hdr_m = max(os.path.getmtime(f) for f in glob.glob(os.path.join(CSRC, "*.cuh")) +
+                glob.glob(os.path.join(ROOT, "include", "*.h")))
+    if os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(src), hdr_m):
+        return obj
+    cmd = [_nvcc(), *ARCH, *[f for f in NVCC_FLAGS if f != "--use_fast_math=false"], "-I", os.path.join(ROOT, "include"),
+           "-c", src, "-o", obj]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    with open(os.path.join(log_dir, os.path.basename(src) + ".log"), "w") as f:
+        f.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
+    if r.returncode != 0:
+        raise RuntimeError(f"nvcc failed for {src}:\n{r.stderr[-4000:]}")
+    return obj
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    if not force and not needs_build():
+        return LIB
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    log_dir = os.path.join(OUT_DIR, "logs")
+    os.makedirs(log_dir, exist_ok=True)
+    if force:
+        for o in glob.glob(os.path.join(OBJ_DIR, "*.o")):
+            os.remove(o)
+    with ThreadPoolExecutor(max_workers=8) as ex:
+        objs = list(ex.map(lambda s: _compile(s, log_dir), sources()))
+    cmd = [_nvcc(), *ARCH, "-shared", "-o", LIB + ".tmp", *objs, "-lcuda"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"link failed:\n{r.stderr[-4000:]}")
+    os.replace(LIB + ".tmp", LIB)
+    if verbose:
+        print(f"built {LIB} from {len(objs)} objects")
+    return LIB
+
+
+if __name__ == "__main__":
+    build(force="--force" in sys.argv, verbose=True)

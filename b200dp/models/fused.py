@@ -1,0 +1,269 @@
+"""Native LeNet runner: the whole training step as a short fixed sequence of
+hand-written sm_100a kernels over flat arenas, optionally replayed from a CUDA graph.
+
+Step = 9 launches (reference: ~50 ATen/cuDNN/cuBLAS kernels + 10 NCCL all-reduces
++ 10 divides + the optimizer's elementwise kernels, train.py:45-51):
+
+    main stream                                   side stream (overlapped)
+    ---------------------------------------------  -----------------------------
+    conv1 fwd   (normalise+upsample+conv+act+pool)
+    conv2 fwd   (conv+act+pool)
+    conv3 fwd   (GEMM+bias+act)
+    fc1   fwd   (GEMM+bias+act)
+    head tail   (fc2+softmax+loss+dlogits+dz1)
+    head bwd A  {dW fc2, dW fc1, dZ3}  ----------> reduce+update bucket 0 (FC.*)
+    head bwd B  {dW conv3, dP2}        ----------> reduce+update bucket 1 (ConvNet.7)
+    conv bwd    (pool/act bwd, dgrad, 2x wgrad) -> reduce+update bucket 2 (ConvNet.1, .4)
+
+The reduce+update launch is the fused P2P all-reduce + average + optimizer
+kernel (csrc/reduce_update.cu); with world size 1 it degenerates to the
+optimizer update.  ``state_dict`` keys/shapes are the reference's because the
+parameters are views of an eager :class:`LeNet` re-pointed into the arena.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from ..data.synthetic import MNIST_SPEC, ImageSpec
+from ..ops import native
+from ..optim.flat import FlatOptimizer, OptHyper
+from ..parallel.arena import FlatArena, lenet_groups
+from ..parallel.p2p import P2PComm
+from .lenet import LeNet, LeNetConfig
+
+_LOSS_MODES = {"ref": 0, "xent": 1}
+
+
+class NativeLeNet:
+    """Buffers + kernel launch sequences for one model replica on one GPU."""
+
+    def __init__(self, cfg: LeNetConfig, batch: int, device: torch.device, *, loss_mode: str = "ref",
+                 spec: ImageSpec = MNIST_SPEC, module: Optional[LeNet] = None):
+        native.load()
+        self.cfg, self.B, self.device, self.spec = cfg, int(batch), torch.device(device), spec
+        self.loss_mode = _LOSS_MODES[loss_mode]
+        self.module = module if module is not None else LeNet(cfg)
+        self.module.to(self.device)
+        names = [n for n, _ in self.module.named_parameters()]
+        self.arena = FlatArena(self.module, lenet_groups(names), self.device)
+        L = self.arena.layout
+        self.w = {n: L.view(self.arena.param, n) for n in names}
+        self.g = {n: L.view(self.arena.grad, n) for n in names}
+        self.bucket_fc, self.bucket_c3, self.bucket_conv = L.buckets[0], L.buckets[1], L.buckets[2]
+        B, c = self.B, cfg
+        f32 = dict(dtype=torch.float32, device=self.device)
+        u8 = dict(dtype=torch.uint8, device=self.device)
+        self.p1 = torch.empty(B, c.c1, 14, 14, **f32)
+        self.idx1 = torch.empty(B, c.c1, 14, 14, **u8)
+        self.p2 = torch.empty(B, c.c2, 5, 5, **f32)
+        self.idx2 = torch.empty(B, c.c2, 5, 5, **u8)
+        self.a3 = torch.empty(B, c.c3, **f32)
+        self.h1 = torch.empty(B, c.f1, **f32)
+        self.probs = torch.empty(B, c.num_classes, **f32)
+        self.loss_rows = torch.empty(B, **f32)
+        self.loss = torch.zeros(1, **f32)
+        self.dlogits = torch.empty(B, c.num_classes, **f32)
+        self.dz1 = torch.empty(B, c.f1, **f32)
+        self.dz3 = torch.empty(B, c.c3, **f32)
+        self.dp2 = torch.empty(B, c.c2 * 25, **f32)
+        self.ticket = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.eval_acc = torch.zeros(2, dtype=torch.float64, device=self.device)
+        self.n_partials = native.conv_bwd_num_partials(self.dims(B))
+        self.partial_stride = self.bucket_conv.numel
+        # scratch: one partial-gradient row per conv-backward CTA (zeroed once: padding columns stay 0)
+        self.partials = torch.zeros(self.n_partials, self.partial_stride, **f32)
+        s0 = self.bucket_conv.start
+        sl = L.slots
+        self.conv_offsets = tuple(sl[k].offset - s0 for k in
+                                  ("ConvNet.1.weight", "ConvNet.1.bias", "ConvNet.4.weight", "ConvNet.4.bias"))
+        self.launches_per_step = 0
+
+    def dims(self, b: int) -> native.Dims:
+        c = self.cfg
+        return native.Dims(b, c.in_ch, c.in_hw, c.c1, c.c2, c.c3, c.f1, c.num_classes)
+
+    # ---- forward ----------------------------------------------------------------
+    def forward(self, x: torch.Tensor, y: torch.Tensor, train: bool) -> None:
+        b = x.shape[0]
+        assert b <= self.B and x.is_contiguous() and y.dtype == torch.int64
+        d, w = self.dims(b), self.w
+        native.conv1_fwd(x, w["ConvNet.1.weight"], w["ConvNet.1.bias"], self.p1, self.idx1 if train else None,
+                         d, self.spec.mean, self.spec.std)
+        native.conv2_fwd(self.p1, w["ConvNet.4.weight"], w["ConvNet.4.bias"], self.p2,
+                         self.idx2 if train else None, d)
+        native.linear_fwd(self.p2[:b].view(b, -1), w["ConvNet.7.weight"].view(self.cfg.c3, -1),
+                          w["ConvNet.7.bias"], self.a3[:b], 1)
+        native.linear_fwd(self.a3[:b], w["FC.0.weight"], w["FC.0.bias"], self.h1[:b], 1)
+        native.head_tail(self.h1[:b], w["FC.2.weight"], w["FC.2.bias"], y, self.loss_mode, self.probs[:b],
+                         self.loss_rows[:b], self.loss, self.dlogits[:b] if train else None,
+                         self.dz1[:b] if train else None, None if train else self.eval_acc, self.ticket)
+
+    # ---- backward, in three launches; a callback fires as each bucket's gradients complete ----
+    def backward(self, x: torch.Tensor, on_bucket=None) -> None:
+        b, c, w, g = x.shape[0], self.cfg, self.w, self.g
+        d = self.dims(b)
+        k3 = c.c2 * 25
+        native.linear_bwd_group([
+            native.bwd_problem(1, self.dlogits, self.h1, None, g["FC.2.weight"], g["FC.2.bias"], b, c.num_classes, c.f1),
+            native.bwd_problem(1, self.dz1, self.a3, None, g["FC.0.weight"], g["FC.0.bias"], b, c.f1, c.c3),
+            native.bwd_problem(0, self.dz1, w["FC.0.weight"], self.a3, self.dz3, None, b, c.f1, c.c3),
+        ])
+        if on_bucket:
+            on_bucket(0)
+        native.linear_bwd_group([
+            native.bwd_problem(1, self.dz3, self.p2, None, g["ConvNet.7.weight"], g["ConvNet.7.bias"], b, c.c3, k3),
+            native.bwd_problem(0, self.dz3, w["ConvNet.7.weight"], None, self.dp2, None, b, c.c3, k3),
+        ])
+        if on_bucket:
+            on_bucket(1)
+        ow1, ob1, ow2, ob2 = self.conv_offsets
+        native.conv_bwd(x, self.spec.mean, self.spec.std, self.p1, self.idx1, self.p2, self.idx2, self.dp2,
+                        w["ConvNet.4.weight"], self.partials, self.partial_stride, ow1, ob1, ow2, ob2, d)
+        if on_bucket:
+            on_bucket(2)
+
+
+class NativeStepper:
+    """Engine-facing stepper: ``train_step`` / ``eval_batch`` / ``eval_result`` on native kernels,
+    gradient reduction + optimizer fused in the P2P kernel, step replayed from CUDA graphs."""
+
+    name = "native"
+    MAX_GRAPHS = 8
+
+    def __init__(self, ctx, cfg: LeNetConfig, hyper: OptHyper, *, batch: int, loss_mode: str = "ref",
+                 spec: ImageSpec = MNIST_SPEC, algo: str = "auto", graph: bool = True, overlap: bool = True,
+                 dtype: str = "bf16", module: Optional[LeNet] = None):
+        self.ctx, self.cfg = ctx, cfg
+        self.device = ctx.device
+        self.net = NativeLeNet(cfg, batch, self.device, loss_mode=loss_mode, spec=spec, module=module)
+        self.model = self.net.module
+        self.arena = self.net.arena
+        self.optimizer = FlatOptimizer(self.arena.param, self.arena.grad, hyper)
+        self.world = ctx.world_size
+        self.comm = P2PComm(self.arena.layout.total, ctx.rank, self.world, algo) if self.world > 1 else None
+        self.use_graph, self.overlap = graph, overlap
+        self.side = torch.cuda.Stream(device=self.device) if overlap else None
+        self.hyper_dev = torch.zeros(8, dtype=torch.float32, device=self.device)
+        self.hyper_host = torch.zeros(8, dtype=torch.float32).pin_memory()
+        self._hyper_cache: Optional[Tuple] = None
+        self.step_counter = torch.zeros(4, dtype=torch.int32, device=self.device)
+        self._graphs: Dict[Tuple[int, int, int], torch.cuda.CUDAGraph] = {}
+        self._static_x: Optional[torch.Tensor] = None
+        self._static_y: Optional[torch.Tensor] = None
+        self._warm = 0
+        self.launches_per_step = 11   # 5 fwd + 3 bwd + 3 reduce/update
+
+    # ---- optimizer scalars live on the device so graph replays see scheduler changes ----
+    def _sync_hyper(self) -> None:
+        h = self.optimizer.hyper
+        if h.kind == "adadelta":
+            vec = (self.optimizer.lr, h.rho, h.eps, 0.0, h.weight_decay)
+        elif h.kind == "sgd":
+            vec = (self.optimizer.lr, h.momentum, 1.0 if h.nesterov else 0.0, 0.0, h.weight_decay)
+        else:
+            vec = (self.optimizer.lr, h.beta1, h.beta2, h.eps, h.weight_decay)
+        if vec != self._hyper_cache:
+            self.hyper_host[:5] = torch.tensor(vec, dtype=torch.float32)
+            self.hyper_dev.copy_(self.hyper_host, non_blocking=True)
+            self._hyper_cache = vec
+
+    def _reduce_update(self, bucket_index: int) -> None:
+        net, opt = self.net, self.optimizer
+        b = self.arena.layout.buckets[bucket_index]
+        is_conv = bucket_index == 2
+        native.reduce_update(self.arena.param, self.arena.grad, opt.state0, opt.state1, None, b.start, b.numel,
+                             net.partials if is_conv else None, net.n_partials if is_conv else 0,
+                             net.partial_stride if is_conv else 0, opt.hyper.code(), self.hyper_dev,
+                             self.step_counter, bucket_index == 2, self.comm.struct if self.comm else None)
+
+    def _step_body(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        main = torch.cuda.current_stream(self.device)
+        self.net.forward(x, y, train=True)
+
+        def on_bucket(i: int) -> None:
+            if self.side is None:
+                self._reduce_update(i)
+                return
+            self.side.wait_stream(main)
+            with torch.cuda.stream(self.side):
+                self._reduce_update(i)
+
+        self.net.backward(x, on_bucket)
+        if self.side is not None:
+            main.wait_stream(self.side)
+
+    def train_step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        self._sync_hyper()
+        self.optimizer.step_count += 1
+        b = x.shape[0]
+        if not self.use_graph or b != self.net.B:
+            self._step_body(x, y)
+            return self.net.loss
+        if self._warm < 2:                       # lazy module loading etc. must happen outside capture
+            self._step_body(x, y)
+            self._warm += 1
+            return self.net.loss
+        key = (x.data_ptr(), y.data_ptr(), b)
+        gph = self._graphs.get(key)
+        if gph is None:
+            if len(self._graphs) >= self.MAX_GRAPHS:
+                return self._replay_static(x, y)
+            gph = self._capture(x, y)
+            self._graphs[key] = gph
+        gph.replay()
+        return self.net.loss
+
+    def _capture(self, x: torch.Tensor, y: torch.Tensor) -> torch.cuda.CUDAGraph:
+        torch.cuda.synchronize(self.device)
+        gph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gph, capture_error_mode="thread_local"):
+            self._step_body(x, y)
+        return gph
+
+    def _replay_static(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        if self._static_x is None:
+            self._static_x, self._static_y = torch.empty_like(x), torch.empty_like(y)
+            self._graphs[("static",)] = self._capture(self._static_x, self._static_y)
+        self._static_x.copy_(x)
+        self._static_y.copy_(y)
+        self._graphs[("static",)].replay()
+        return self.net.loss
+
+    # ---- eval ----------------------------------------------------------------------
+    def eval_batch(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        self.net.forward(x, y, train=False)
+
+    def eval_result(self, reset: bool = True) -> Tuple[float, int]:
+        vals = self.net.eval_acc.tolist()        # the one D2H of the epoch
+        if reset:
+            self.net.eval_acc.zero_()
+        return float(vals[0]), int(vals[1])
+
+    # ---- bookkeeping -----------------------------------------------------------------
+    def params_changed(self) -> None:
+        """Call after loading a checkpoint: re-seed the device generation counter."""
+        self.step_counter[0] = self.optimizer.step_count
+        self._hyper_cache = None
+
+    def check_error(self) -> None:
+        if int(self.step_counter[2].item()) != 0:
+            raise RuntimeError("a peer rank did not publish its gradients within the spin bound (dead rank?)")
+
+    @torch.no_grad()
+    def replica_divergence(self) -> float:
+        if self.world == 1:
+            return 0.0
+        ref = self.arena.param.clone()
+        dist.broadcast(ref, src=0)
+        d = (self.arena.param - ref).abs().max().reshape(1)
+        dist.all_reduce(d, op=dist.ReduceOp.MAX)
+        return float(d.item())
+
+    def close(self) -> None:
+        self._graphs.clear()
+        if self.comm is not None:
+            self.comm.close()
+            self.comm = None

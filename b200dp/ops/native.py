@@ -1,0 +1,186 @@
+"""ctypes bindings to the in-tree CUDA library (include/b200dp.h, csrc/*.cu).
+
+The library is plain C ABI + raw device pointers, so the binding is a thin
+layer: ``tensor.data_ptr()`` in, ``torch.cuda.current_stream().cuda_stream``
+as the launch stream (so launches are captured by ``torch.cuda.graph``).
+Nothing here falls back to torch ops: if the library is missing on a GPU box
+the import raises (the driver checks that the native code is what ran).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional, Sequence
+
+import torch
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_native", "libb200dp.so")
+_lib = None
+
+
+class Dims(C.Structure):
+    _fields_ = [("batch", C.c_int), ("in_ch", C.c_int), ("in_hw", C.c_int), ("c1", C.c_int),
+                ("c2", C.c_int), ("c3", C.c_int), ("f1", C.c_int), ("ncls", C.c_int)]
+
+
+class BwdProblem(C.Structure):
+    _fields_ = [("kind", C.c_int), ("dy", C.c_void_p), ("w_or_x", C.c_void_p), ("act_prev", C.c_void_p),
+                ("out", C.c_void_p), ("db", C.c_void_p), ("M", C.c_int), ("N", C.c_int), ("K", C.c_int)]
+
+
+class Comm(C.Structure):
+    _fields_ = [("world", C.c_int), ("rank", C.c_int), ("algo", C.c_int),
+                ("stage", C.c_void_p * 8), ("flags", C.c_void_p * 8), ("mc_stage", C.c_void_p),
+                ("arena_len", C.c_int), ("max_slices", C.c_int)]
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def load(build_if_missing: bool = True):
+    """dlopen the library (building it first if the sources are newer / it is absent)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if build_if_missing:
+        from .. import build as _build
+        try:
+            _build.build()
+        except Exception as e:  # no nvcc on this box: use what was shipped
+            if not os.path.exists(_LIB_PATH):
+                raise RuntimeError(f"libb200dp.so is missing and could not be built: {e}") from e
+    if not os.path.exists(_LIB_PATH):
+        raise RuntimeError(f"{_LIB_PATH} not found; run `python -m b200dp.build`")
+    lib = C.CDLL(_LIB_PATH)
+    vp, i, f = C.c_void_p, C.c_int, C.c_float
+    lib.b200dp_last_error.restype = C.c_char_p
+    lib.b200dp_conv1_fwd.argtypes = [vp, i, f, f, vp, vp, vp, vp, Dims, vp]
+    lib.b200dp_conv2_fwd.argtypes = [vp, vp, vp, vp, vp, Dims, vp]
+    lib.b200dp_linear_fwd.argtypes = [vp, vp, vp, vp, i, i, i, i, vp]
+    lib.b200dp_head_tail.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
+    lib.b200dp_linear_bwd_group.argtypes = [C.POINTER(BwdProblem), i, vp]
+    lib.b200dp_conv_bwd_num_partials.argtypes = [Dims]
+    lib.b200dp_conv_bwd.argtypes = [vp, i, f, f, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, Dims, vp]
+    lib.b200dp_reduce_update.argtypes = [vp, vp, vp, vp, vp, i, i, vp, i, i, i, vp, vp, i, C.POINTER(Comm), vp]
+    lib.b200dp_symm_alloc.argtypes = [C.POINTER(vp), C.c_uint64]
+    lib.b200dp_symm_free.argtypes = [vp]
+    lib.b200dp_symm_export.argtypes = [vp, C.c_char_p]
+    lib.b200dp_symm_import.argtypes = [C.c_char_p, C.POINTER(vp)]
+    lib.b200dp_symm_close.argtypes = [vp]
+    lib.b200dp_enable_peer_access.argtypes = [i]
+    _lib = lib
+    return lib
+
+
+def is_loaded() -> bool:
+    return _lib is not None
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load().b200dp_last_error().decode(errors="replace")
+        raise NativeError(f"{what} failed (cuda error {rc}): {msg}")
+
+
+def _p(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _f32(*ts: torch.Tensor) -> None:
+    for t in ts:
+        if t is not None and (t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda):
+            raise TypeError("expected contiguous CUDA float32 tensors")
+
+
+# ---- forward -----------------------------------------------------------------
+def conv1_fwd(x, w, b, p1, idx1, dims: Dims, mean: float, std: float) -> None:
+    _f32(w, b, p1)
+    check(load().b200dp_conv1_fwd(_p(x), int(x.dtype == torch.uint8), mean, std, _p(w), _p(b), _p(p1), _p(idx1),
+                                  dims, _stream()), "conv1_fwd")
+
+
+def conv2_fwd(p1, w, b, p2, idx2, dims: Dims) -> None:
+    _f32(p1, w, b, p2)
+    check(load().b200dp_conv2_fwd(_p(p1), _p(w), _p(b), _p(p2), _p(idx2), dims, _stream()), "conv2_fwd")
+
+
+def linear_fwd(x, w, b, y, act: int) -> None:
+    _f32(x, w, b, y)
+    M, K = x.shape[0], x.numel() // x.shape[0]
+    N = w.shape[0]
+    check(load().b200dp_linear_fwd(_p(x), _p(w), _p(b), _p(y), M, N, K, act, _stream()), "linear_fwd")
+
+
+def head_tail(h1, w, b, target, loss_mode: int, probs, loss_rows, loss_out, dlogits, dz1, eval_acc, ticket) -> None:
+    _f32(h1, w, b, probs, loss_rows, loss_out, dlogits, dz1)
+    B, F1 = h1.shape
+    check(load().b200dp_head_tail(_p(h1), _p(w), _p(b), _p(target), loss_mode, _p(probs), _p(loss_rows),
+                                  _p(loss_out), _p(dlogits), _p(dz1), _p(eval_acc), _p(ticket), B, F1,
+                                  w.shape[0], _stream()), "head_tail")
+
+
+# ---- backward ----------------------------------------------------------------
+def bwd_problem(kind: int, dy, w_or_x, act_prev, out, db, M: int, N: int, K: int) -> BwdProblem:
+    return BwdProblem(kind, _p(dy), _p(w_or_x), _p(act_prev), _p(out), _p(db), M, N, K)
+
+
+def linear_bwd_group(problems: Sequence[BwdProblem]) -> None:
+    arr = (BwdProblem * len(problems))(*problems)
+    check(load().b200dp_linear_bwd_group(arr, len(problems), _stream()), "linear_bwd_group")
+
+
+def conv_bwd_num_partials(dims: Dims) -> int:
+    return int(load().b200dp_conv_bwd_num_partials(dims))
+
+
+def conv_bwd(x, mean, std, p1, idx1, p2, idx2, dp2, w2, partials, stride, off_w1, off_b1, off_w2, off_b2,
+             dims: Dims) -> None:
+    check(load().b200dp_conv_bwd(_p(x), int(x.dtype == torch.uint8), mean, std, _p(p1), _p(idx1), _p(p2),
+                                 _p(idx2), _p(dp2), _p(w2), _p(partials), stride, off_w1, off_b1, off_w2,
+                                 off_b2, dims, _stream()), "conv_bwd")
+
+
+# ---- reduce + update -----------------------------------------------------------
+def reduce_update(param, grad, state0, state1, shadow, start: int, count: int, partials, n_partials: int,
+                  partial_stride: int, opt_kind: int, hyper, step_counter, last_bucket: bool,
+                  comm: Optional[Comm]) -> None:
+    check(load().b200dp_reduce_update(_p(param), _p(grad), _p(state0), _p(state1), _p(shadow), start, count,
+                                      _p(partials), n_partials, partial_stride, opt_kind, _p(hyper),
+                                      _p(step_counter), int(last_bucket),
+                                      C.byref(comm) if comm is not None else None, _stream()), "reduce_update")
+
+
+# ---- symmetric memory ------------------------------------------------------------
+def symm_alloc(nbytes: int) -> int:
+    ptr = C.c_void_p()
+    check(load().b200dp_symm_alloc(C.byref(ptr), nbytes), "symm_alloc")
+    return ptr.value
+
+
+def symm_free(ptr: int) -> None:
+    check(load().b200dp_symm_free(ptr), "symm_free")
+
+
+def symm_export(ptr: int) -> bytes:
+    buf = C.create_string_buffer(64)
+    check(load().b200dp_symm_export(ptr, buf), "symm_export")
+    return buf.raw
+
+
+def symm_import(handle: bytes) -> int:
+    ptr = C.c_void_p()
+    check(load().b200dp_symm_import(handle, C.byref(ptr)), "symm_import")
+    return ptr.value
+
+
+def symm_close(ptr: int) -> None:
+    check(load().b200dp_symm_close(ptr), "symm_close")

@@ -1,0 +1,300 @@
+#!/usr/bin/env python
+"""Headline benchmark: cnn.py (LeNet) data-parallel training throughput, images/sec.
+
+Metric / config are BASELINE.json's: "cnn.py images/sec (device-timed, max over ranks) at
+1/2/4/8 B200", configs[1] = per-GPU batch 256 on synthetic data of train.py's dataset shape
+(1x28x28, 10 classes), weak scaling.  Reference optimizer (Adadelta lr 0.1) and loss
+(nll_loss on softmax probabilities) are kept, and every step runs forward, backward, the
+gradient reduction and the optimizer update.
+
+    python bench.py --gpus 1 --steps 200 --warmup 20
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+           --master-port P bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...   # the unmodified reference from baseline/_ref
+
+Two numbers per run:
+  value  device-timed kernel path: inputs are already on the device (a pool larger than the
+         126 MB L2, cycled), K steps between CUDA events, barrier + synchronize on both sides,
+         max over ranks.
+  e2e    through the public API (NativeStepper.train_step fed by PinnedRingLoader): every step
+         copies its batch from pinned host memory to the device and reads the loss back.
+"""
+from __future__ import annotations
+
+import argparse
+import contextlib
+import io
+import json
+import math
+import os
+import sys
+import time
+import types
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+PER_GPU_BATCH = 256
+L2_BYTES = 126 * 1024 * 1024
+
+
+def _parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=300)
+    p.add_argument("--warmup", type=int, default=30)
+    p.add_argument("--impl", choices=["b200dp", "reference"], default="b200dp")
+    p.add_argument("--config", choices=["lenet_b256", "strong4096", "wide_cifar"], default="lenet_b256")
+    p.add_argument("--optimizer", default="adadelta")
+    p.add_argument("--no-graph", action="store_true")
+    p.add_argument("--no-overlap", action="store_true")
+    p.add_argument("--input", choices=["u8", "f32"], default="u8", help="host->device input format (e2e)")
+    return p.parse_args()
+
+
+def _init_dist(n):
+    """Join the group when launched by torchrun; single process otherwise."""
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    if world != n:
+        if world == 1 and n > 1:
+            raise SystemExit(f"--gpus {n} needs torchrun with --nproc-per-node {n}")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1 or "RANK" in os.environ:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    return rank, world, local, dev
+
+
+def _sync_all():
+    if dist.is_initialized():
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def _max_ranks(ms, dev):
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    return ms
+
+
+def _model_cfg(name):
+    from b200dp.data.synthetic import CIFAR_SPEC, MNIST_SPEC
+    from b200dp.models.lenet import CIFAR_WIDE_LENET, MNIST_LENET
+    if name == "wide_cifar":
+        return CIFAR_WIDE_LENET, CIFAR_SPEC
+    return MNIST_LENET, MNIST_SPEC
+
+
+def run_own(args):
+    from b200dp.data.synthetic import PinnedRingLoader
+    from b200dp.models.fused import NativeStepper
+    from b200dp.ops import native
+    from b200dp.optim.flat import OptHyper
+    from b200dp.parallel.launch import RankContext
+    from b200dp.utils.clocks import ClockSampler
+
+    rank, world, local, dev = _init_dist(args.gpus)
+    cfg, spec = _model_cfg(args.config)
+    batch = PER_GPU_BATCH if args.config != "strong4096" else math.ceil(4096 / world)
+    ctx = RankContext(rank, world, local, dev, "nccl")
+    torch.manual_seed(5)
+    stepper = NativeStepper(ctx, cfg, OptHyper(args.optimizer, lr=0.1 if args.optimizer == "adadelta" else 0.01),
+                            batch=batch, loss_mode="ref", spec=spec, graph=not args.no_graph,
+                            overlap=not args.no_overlap)
+    K, W = args.steps, args.warmup
+
+    # ---- device-resident input pool larger than L2, cycled (timing rule) ----
+    img_bytes = spec.channels * spec.height * spec.width
+    n_pool = L2_BYTES // (batch * img_bytes) + 8
+    g = torch.Generator(device="cpu").manual_seed(1234 + rank)
+    pool_x = torch.randint(0, 256, (n_pool, batch, spec.channels, spec.height, spec.width), dtype=torch.uint8,
+                           generator=g).to(dev)
+    pool_y = torch.randint(0, spec.classes, (n_pool, batch), generator=g).to(dev)
+    sx, sy = torch.empty_like(pool_x[0]), torch.empty_like(pool_y[0])
+
+    def dev_step(i):
+        j = i % n_pool
+        sx.copy_(pool_x[j], non_blocking=True)
+        sy.copy_(pool_y[j], non_blocking=True)
+        return stepper.train_step(sx, sy)
+
+    for i in range(W):
+        dev_step(i)
+    _sync_all()
+    sampler = ClockSampler(local).start() if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(K):
+        dev_step(W + i)
+    e1.record()
+    _sync_all()
+    ms = _max_ranks(e0.elapsed_time(e1), dev)
+    clocks = sampler.stop() if sampler else None
+    stepper.check_error()
+    loss_dev = float(stepper.net.loss)
+
+    # ---- end to end through the public API: pinned host -> device every step, loss read back ----
+    n_host = max(2 * (K + W), 64) * batch
+    n_host = min(n_host, 200_000)
+    hx = torch.randint(0, 256, (n_host, spec.channels, spec.height, spec.width), dtype=torch.uint8, generator=g)
+    hy = torch.randint(0, spec.classes, (n_host,), generator=g)
+    loader = PinnedRingLoader(hx, hy, 0, n_host, batch, spec, shuffle=True, fmt=args.input, device=dev,
+                              seed=rank, drop_last=True)
+    loss_ring = torch.zeros(K + W + 8, dtype=torch.float32).pin_memory()
+
+    def e2e_epoch(n_steps, base):
+        done = 0
+        while done < n_steps:
+            for x, y in loader:
+                loss = stepper.train_step(x, y)
+                loss_ring[base + done:base + done + 1].copy_(loss, non_blocking=True)   # D2H every step
+                done += 1
+                if done >= n_steps:
+                    break
+        return done
+
+    e2e_epoch(W, 0)
+    _sync_all()
+    e0.record()
+    t0 = time.perf_counter()
+    e2e_epoch(K, W)
+    e1.record()
+    _sync_all()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    e2e_ms = _max_ranks(max(e0.elapsed_time(e1), wall_ms), dev)
+    stepper.check_error()
+    loss_e2e = float(loss_ring[W + K - 1])
+    div = stepper.replica_divergence()
+
+    if rank == 0:
+        imgs = batch * world * K
+        out = {
+            "metric": "cnn.py images/sec (device-timed, max over ranks)",
+            "value": imgs / (ms / 1e3), "unit": "images/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True,
+            "scaling": "strong" if args.config == "strong4096" else "weak",
+            "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": "b200dp",
+            "config": {"model": "cnn.py LeNet" if args.config != "wide_cifar" else "cnn.py LeNet 4x wide, CIFAR-shaped",
+                       "global_batch": batch * world, "per_gpu_batch": batch, "seq_len": None,
+                       "input": f"{spec.channels}x{spec.height}x{spec.width}",
+                       "parallelism": f"dp{world}", "optimizer": args.optimizer, "loss": "ref (nll on softmax probs)",
+                       "l2": f"inputs cycle through a {n_pool * batch * img_bytes >> 20} MiB device pool (> 126 MiB L2)",
+                       "cuda_graph": not args.no_graph, "overlap": not args.no_overlap,
+                       "allreduce": "fused one-shot P2P reduce+average+update kernel" if world > 1 else "n/a (1 GPU)"},
+            "clocks": clocks,
+            "e2e": {"value": imgs / (e2e_ms / 1e3), "unit": "images/s", "ms_per_step": e2e_ms / K,
+                    "h2d_bytes_per_step": loader.h2d_bytes_per_batch, "d2h_bytes_per_step": 4,
+                    "input_format": args.input},
+            "gpu_launches": stepper.launches_per_step * K,
+            "final_loss": {"device_path": loss_dev, "e2e_path": loss_e2e},
+            "replica_divergence": div,
+            "native_lib": os.path.relpath(native.lib_path(), ROOT),
+        }
+        print(json.dumps(out), flush=True)
+    stepper.close()
+    if dist.is_initialized():
+        dist.destroy_process_group()
+
+
+class _RefLoader:
+    """Feeds the reference's train() (train.py:42-57) W+K pinned fp32 batches of its dataset shape and
+    brackets the timed region with CUDA events from inside the iteration."""
+
+    def __init__(self, xs, ys, batch, warmup, steps):
+        self.xs, self.ys, self.batch, self.W, self.K = xs, ys, batch, warmup, steps
+        self.dataset = list(range((warmup + steps) * batch))
+        self.e0, self.e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        self.t0 = 0.0
+
+    def __len__(self):
+        return self.W + self.K
+
+    def __iter__(self):
+        n = self.xs.shape[0]
+        for i in range(self.W + self.K):
+            if i == self.W:
+                _sync_all()
+                self.e0.record()
+                self.t0 = time.perf_counter()
+            j = i % n
+            yield self.xs[j], self.ys[j]
+
+
+def run_reference(args):
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isfile(os.path.join(ref_dir, "train.py")):
+        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref not installed (see DESIGN.md)"}))
+        return
+    if args.config != "lenet_b256":
+        print(json.dumps({"impl": "reference", "unavailable": "the reference has a single fixed model/config"}))
+        return
+    rank, world, local, dev = _init_dist(args.gpus)
+    if not dist.is_initialized():   # the reference's average_gradients() needs a group even at size 1
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", str(29500 + os.getpid() % 2000))
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
+    sys.path.insert(0, ref_dir)
+    import train as ref_train          # unmodified reference modules
+    from cnn import LeNet as RefLeNet
+    from b200dp.utils.clocks import ClockSampler
+
+    torch.manual_seed(5)
+    torch.cuda.manual_seed(5)
+    batch, K, W = PER_GPU_BATCH, args.steps, args.warmup
+    n_pool = 64
+    g = torch.Generator().manual_seed(1234 + rank)
+    xs = torch.randn(n_pool, batch, 1, 28, 28, generator=g).pin_memory()      # what ToTensor+Normalize yields
+    ys = torch.randint(0, 10, (n_pool, batch), generator=g).pin_memory()
+    model = RefLeNet().cuda(local)                                             # train.py:98
+    optimizer = torch.optim.Adadelta(model.parameters(), lr=0.1)               # train.py:99
+    ref_args = types.SimpleNamespace(log_interval=15, dry_run=False)           # train.py defaults
+    loader = _RefLoader(xs, ys, batch, W, K)
+    sampler = ClockSampler(local).start() if rank == 0 else None
+    with contextlib.redirect_stdout(io.StringIO()):                            # keep its rank-0 log lines off stdout
+        ref_train.train(ref_args, model, local, loader, optimizer, 1)          # the reference's own loop
+    loader.e1.record()
+    _sync_all()
+    wall_ms = (time.perf_counter() - loader.t0) * 1e3
+    ms = _max_ranks(loader.e0.elapsed_time(loader.e1), dev)
+    clocks = sampler.stop() if sampler else None
+    if rank == 0:
+        imgs = batch * world * K
+        h2d = batch * 784 * 4 + batch * 8
+        print(json.dumps({
+            "metric": "cnn.py images/sec (device-timed, max over ranks)",
+            "value": imgs / (ms / 1e3), "unit": "images/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "fp32", "data": "synthetic", "impl": "reference",
+            "config": {"model": "cnn.py LeNet", "global_batch": batch * world, "per_gpu_batch": batch,
+                       "seq_len": None, "input": "1x28x28", "parallelism": f"dp{world}",
+                       "optimizer": "adadelta", "loss": "ref (nll on softmax probs)",
+                       "path": "baseline/_ref train.train() + average_gradients(), NCCL, stock code path",
+                       "l2": "inputs come from pinned host memory every step (never L2-resident)"},
+            "clocks": clocks,
+            "e2e": {"value": imgs / (max(ms, wall_ms) / 1e3), "unit": "images/s",
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4 / 15,
+                    "note": "the reference loop is end to end by construction: synchronous H2D each step, "
+                            "loss.item() every 15 steps on rank 0"},
+            "gpu_launches": 0,
+        }), flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = _parse()
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": a.impl, "unavailable": "no CUDA device visible"}))
+        sys.exit(0)
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_own(a)

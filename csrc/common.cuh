@@ -1,0 +1,80 @@
+// Shared device/host helpers for the b200dp CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../include/b200dp.h"
+
+#define LEAKY_SLOPE 0.2f
+
+namespace b200dp {
+
+void set_last_error(const char* fmt, ...);
+
+#define B200DP_CHECK(expr)                                                              \
+    do {                                                                                \
+        cudaError_t _e = (expr);                                                        \
+        if (_e != cudaSuccess) {                                                        \
+            ::b200dp::set_last_error("%s:%d %s -> %s", __FILE__, __LINE__, #expr,       \
+                                     cudaGetErrorString(_e));                           \
+            return (int)_e;                                                             \
+        }                                                                               \
+    } while (0)
+
+#define B200DP_REQUIRE(cond, msg)                                                       \
+    do {                                                                                \
+        if (!(cond)) {                                                                  \
+            ::b200dp::set_last_error("%s:%d requirement failed: %s (%s)", __FILE__,     \
+                                     __LINE__, #cond, msg);                             \
+            return (int)cudaErrorInvalidValue;                                          \
+        }                                                                               \
+    } while (0)
+
+__device__ __forceinline__ float leaky(float v) { return v > 0.f ? v : LEAKY_SLOPE * v; }
+// derivative of LeakyReLU evaluated from the *activated* value (sign is preserved)
+__device__ __forceinline__ float leaky_grad_from_act(float a) { return a > 0.f ? 1.f : LEAKY_SLOPE; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Input pre-processing shared by conv1 forward and conv1 wgrad (which recomputes
+// the 32x32 image instead of storing it): ToTensor+Normalize (reference train.py:85)
+// then UpsamplingBilinear2d(size=32), align_corners=True (reference cnn.py:9).
+__device__ __forceinline__ float load_pixel(const void* x, int is_u8, long idx, float mean, float std) {
+    if (is_u8) {
+        float v = (float)((const uint8_t*)x)[idx];
+        return __fdiv_rn(__fdiv_rn(v, 255.f) - mean, std);
+    }
+    return ((const float*)x)[idx];
+}
+
+// Fill dst[32*32] from a src[hw*hw] plane held in shared memory.
+__device__ __forceinline__ void upsample32_plane(const float* src, int hw, float* dst, int tid, int nthreads) {
+    if (hw == 32) {
+        for (int i = tid; i < 1024; i += nthreads) dst[i] = src[i];
+        return;
+    }
+    const float scale = (float)(hw - 1) / 31.f;
+    for (int i = tid; i < 1024; i += nthreads) {
+        int y = i >> 5, x = i & 31;
+        float h1r = scale * (float)y, w1r = scale * (float)x;
+        int h1 = (int)h1r, w1 = (int)w1r;
+        int h1p = (h1 < hw - 1) ? 1 : 0, w1p = (w1 < hw - 1) ? 1 : 0;
+        float h1l = h1r - (float)h1, h0l = 1.f - h1l;
+        float w1l = w1r - (float)w1, w0l = 1.f - w1l;
+        const float* r0 = src + h1 * hw + w1;
+        const float* r1 = r0 + h1p * hw;
+        dst[i] = h0l * (w0l * r0[0] + w1l * r0[w1p]) + h1l * (w0l * r1[0] + w1l * r1[w1p]);
+    }
+}
+
+}  // namespace b200dp

@@ -1,0 +1,259 @@
+// Fused convolution backward for the LeNet-sized model, CUDA-core path: ONE launch per step does
+//   pool2-bwd + LeakyReLU-bwd -> conv2 dgrad -> pool1-bwd + LeakyReLU-bwd,
+//   conv2 wgrad + bgrad (exploiting that only 1 of 4 dZ2 entries per pool window is non-zero),
+//   conv1 wgrad + bgrad (the 32x32 input is recomputed from the raw image, never stored).
+// conv1 dgrad is never needed (the input requires no gradient).
+//
+// Replaces the autograd backward of reference cnn.py:9-15 (train.py:49): ~12 ATen/cuDNN kernels.
+//
+// A CTA owns images cta, cta+grid, ... and keeps its weight-gradient partial sums in registers;
+// at the end it writes ONE row of `partials` (the scratch buffer; layout = the arena layout of
+// the conv bucket, so column i of a row is arena element bucket_start+i).  Rows are summed in
+// fixed order by b200dp_reduce_update -> bit-reproducible gradients, no atomics.
+#include "common.cuh"
+
+namespace b200dp {
+
+constexpr int CB_NT = 256;
+constexpr int CB_MAX_PARTIALS = 128;
+constexpr int ZP = 18;  // 10x10 conv2-output map zero-padded by 4 on each side
+
+struct ConvBwdArgs {
+    const void* x; int in_is_u8; int in_hw; float mean, std;
+    const float* p1; const uint8_t* idx1;
+    const float* p2; const uint8_t* idx2; const float* dp2;
+    const float* w2;
+    float* partials; int partial_stride;
+    int off_w1, off_b1, off_w2, off_b2;
+    int B;
+};
+
+template <int C0, int C1, int C2>
+struct ConvBwdCfg {
+    static constexpr int W2N = C2 * C1 * 25;
+    static constexpr int W1N = C1 * C0 * 25;
+    static constexpr int W2_PER_THREAD = (W2N + CB_NT - 1) / CB_NT;
+    static constexpr int W1_PER_THREAD = (W1N + CB_NT - 1) / CB_NT;
+    static constexpr int OG = 4;                       // oc groups in the dgrad phase
+    static constexpr int C1P = (C1 + 1) / 2 * 2;        // ic padded to even for float2 weight reads
+    static_assert(C2 % OG == 0, "C2 must split into 4 groups");
+    static_assert(49 * OG <= CB_NT, "dgrad mapping needs 196 threads");
+    static_assert(C1 <= CB_NT / 32, "one warp per conv1 channel for the bias gradient");
+    // shared memory carve-up (floats unless noted)
+    static constexpr int F_X0 = C0 * 1024, F_RAW = C0 * 1024, F_P1 = C1 * 196, F_DZ2 = C2 * ZP * ZP,
+                         F_W2F = C2 * 25 * C1P, F_PART = OG * C1 * 196, F_G1 = C1 * 196, F_G2 = C2 * 25,
+                         I_POS2 = C2 * 25;
+    static constexpr size_t SMEM = (size_t)(F_X0 + F_RAW + F_P1 + F_DZ2 + F_W2F + F_PART + F_G1 + F_G2 + I_POS2) * 4
+                                   + (size_t)(C1 * 196 + 15) / 16 * 16;
+};
+
+template <int C0, int C1, int C2>
+__global__ void __launch_bounds__(CB_NT) conv_bwd_kernel(ConvBwdArgs a) {
+    using C = ConvBwdCfg<C0, C1, C2>;
+    extern __shared__ __align__(16) float smem[];
+    float* sX0 = smem;
+    float* sRaw = sX0 + C::F_X0;
+    float* sP1 = sRaw + C::F_RAW;
+    float* sdZ2 = sP1 + C::F_P1;
+    float* sW2f = sdZ2 + C::F_DZ2;     // [oc][u*5+v][C1P], flipped taps: W2[oc][ic][(4-u)*5+(4-v)]
+    float* sPart = sW2f + C::F_W2F;    // [OG][C1][196]
+    float* sG1 = sPart + C::F_PART;    // dL/d(conv1 pre-activation) at the pooled argmax, [C1][196]
+    float* sG2 = sG1 + C::F_G1;        // dL/d(conv2 pre-activation) at the pooled argmax, [C2][25]
+    int* sPos2 = reinterpret_cast<int*>(sG2 + C::F_G2);            // y*,x* packed: y*<<8 | x*
+    uint8_t* sIdx1 = reinterpret_cast<uint8_t*>(sPos2 + C::I_POS2);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int hw = a.in_hw, n_in = hw * hw;
+
+    // flipped / transposed conv2 weights, staged once per CTA
+    for (int i = tid; i < C2 * 25 * C::C1P; i += CB_NT) {
+        int ic = i % C::C1P, r = i / C::C1P, t = r % 25, oc = r / 25;
+        int u = t / 5, v = t - u * 5;
+        sW2f[i] = (ic < C1) ? a.w2[((long)oc * C1 + ic) * 25 + (4 - u) * 5 + (4 - v)] : 0.f;
+    }
+
+    float acc_w2[C::W2_PER_THREAD];
+    float acc_w1[C::W1_PER_THREAD];
+#pragma unroll
+    for (int j = 0; j < C::W2_PER_THREAD; ++j) acc_w2[j] = 0.f;
+#pragma unroll
+    for (int j = 0; j < C::W1_PER_THREAD; ++j) acc_w1[j] = 0.f;
+    float acc_b2 = 0.f;   // thread tid < C2
+    float acc_b1 = 0.f;   // lane 0 of warp w < C1
+
+    for (int img = blockIdx.x; img < a.B; img += gridDim.x) {
+        __syncthreads();  // previous image's readers are done with the shared buffers
+        // ---- phase A: loads ----
+        for (int i = tid; i < C0 * n_in; i += CB_NT)
+            sRaw[i] = load_pixel(a.x, a.in_is_u8, (long)img * C0 * n_in + i, a.mean, a.std);
+        for (int i = tid; i < C1 * 196; i += CB_NT) {
+            sP1[i] = a.p1[(long)img * C1 * 196 + i];
+            sIdx1[i] = a.idx1[(long)img * C1 * 196 + i];
+        }
+        for (int i = tid; i < C2 * 25; i += CB_NT) {
+            const long o = (long)img * C2 * 25 + i;
+            const int pp = i % 25, py = pp / 5, px = pp - py * 5, k = a.idx2[o];
+            sG2[i] = a.dp2[o] * leaky_grad_from_act(a.p2[o]);
+            sPos2[i] = ((2 * py + (k >> 1)) << 8) | (2 * px + (k & 1));
+        }
+        for (int i = tid; i < C::F_DZ2; i += CB_NT) sdZ2[i] = 0.f;
+        __syncthreads();
+        // ---- phase B: input recompute, scatter dZ2 ----
+        for (int c = 0; c < C0; ++c) upsample32_plane(sRaw + c * n_in, hw, sX0 + c * 1024, tid, CB_NT);
+        for (int i = tid; i < C2 * 25; i += CB_NT) {
+            const int oc = i / 25, ps = sPos2[i];
+            sdZ2[oc * ZP * ZP + ((ps >> 8) + 4) * ZP + (ps & 255) + 4] = sG2[i];
+        }
+        __syncthreads();
+        // ---- phase C: conv2 dgrad, dense correlation of padded dZ2 with flipped weights ----
+        if (tid < 49 * C::OG) {
+            const int blk = tid % 49, og = tid / 49;
+            const int by = blk / 7, bx = blk - by * 7;
+            float acc[C1][4];
+#pragma unroll
+            for (int ic = 0; ic < C1; ++ic) acc[ic][0] = acc[ic][1] = acc[ic][2] = acc[ic][3] = 0.f;
+#pragma unroll 1
+            for (int oo = 0; oo < C2 / C::OG; ++oo) {
+                const int oc = og * (C2 / C::OG) + oo;
+                const float* zp = sdZ2 + oc * ZP * ZP + (2 * by) * ZP + 2 * bx;
+                float patch[6][6];
+#pragma unroll
+                for (int r = 0; r < 6; ++r)
+#pragma unroll
+                    for (int c2 = 0; c2 < 3; ++c2) {
+                        float2 v = *reinterpret_cast<const float2*>(zp + r * ZP + 2 * c2);
+                        patch[r][2 * c2] = v.x; patch[r][2 * c2 + 1] = v.y;
+                    }
+                const float* wp = sW2f + oc * 25 * C::C1P;
+#pragma unroll
+                for (int u = 0; u < 5; ++u)
+#pragma unroll
+                    for (int v = 0; v < 5; ++v) {
+                        float wv[C::C1P];
+#pragma unroll
+                        for (int q = 0; q < C::C1P / 2; ++q) {
+                            float2 t2 = *reinterpret_cast<const float2*>(wp + (u * 5 + v) * C::C1P + 2 * q);
+                            wv[2 * q] = t2.x; wv[2 * q + 1] = t2.y;
+                        }
+#pragma unroll
+                        for (int ic = 0; ic < C1; ++ic) {
+                            acc[ic][0] = fmaf(wv[ic], patch[u][v], acc[ic][0]);
+                            acc[ic][1] = fmaf(wv[ic], patch[u][v + 1], acc[ic][1]);
+                            acc[ic][2] = fmaf(wv[ic], patch[u + 1][v], acc[ic][2]);
+                            acc[ic][3] = fmaf(wv[ic], patch[u + 1][v + 1], acc[ic][3]);
+                        }
+                    }
+            }
+#pragma unroll
+            for (int ic = 0; ic < C1; ++ic) {
+                float* dst = sPart + (og * C1 + ic) * 196 + (2 * by) * 14 + 2 * bx;
+                dst[0] = acc[ic][0]; dst[1] = acc[ic][1]; dst[14] = acc[ic][2]; dst[15] = acc[ic][3];
+            }
+        }
+        // ---- phase E (independent of C): conv2 wgrad over the 25 non-zero positions per channel ----
+#pragma unroll
+        for (int j = 0; j < C::W2_PER_THREAD; ++j) {
+            const int o = tid + j * CB_NT;
+            if (o < C::W2N) {
+                const int t = o % 25, r = o / 25, ic = r % C1, oc = r / C1;
+                const int ky = t / 5, kx = t - ky * 5;
+                const float* pin = sP1 + ic * 196 + ky * 14 + kx;
+                float s = 0.f;
+#pragma unroll 5
+                for (int pp = 0; pp < 25; ++pp) {
+                    const int ps = sPos2[oc * 25 + pp];
+                    s = fmaf(sG2[oc * 25 + pp], pin[(ps >> 8) * 14 + (ps & 255)], s);
+                }
+                acc_w2[j] += s;
+            }
+        }
+        if (tid < C2) {
+            float s = 0.f;
+            for (int pp = 0; pp < 25; ++pp) s += sG2[tid * 25 + pp];
+            acc_b2 += s;
+        }
+        __syncthreads();
+        // ---- phase D: sum the dgrad groups (fixed order), apply pool1-bwd mask -> g1 ----
+        for (int i = tid; i < C1 * 196; i += CB_NT) {
+            float dp1 = 0.f;
+#pragma unroll
+            for (int g = 0; g < C::OG; ++g) dp1 += sPart[g * C1 * 196 + i];
+            sG1[i] = dp1 * leaky_grad_from_act(sP1[i]);
+        }
+        __syncthreads();
+        // ---- phase F: conv1 wgrad over the 196 non-zero positions per channel ----
+#pragma unroll
+        for (int j = 0; j < C::W1_PER_THREAD; ++j) {
+            const int o = tid + j * CB_NT;
+            if (o < C::W1N) {
+                const int t = o % 25, r = o / 25, i0 = r % C0, c = r / C0;
+                const int ky = t / 5, kx = t - ky * 5;
+                const float* xin = sX0 + i0 * 1024 + ky * 32 + kx;
+                float s = 0.f;
+#pragma unroll 4
+                for (int pp = 0; pp < 196; ++pp) {
+                    const int py = pp / 14, px = pp - py * 14, k = sIdx1[c * 196 + pp];
+                    s = fmaf(sG1[c * 196 + pp], xin[(2 * py + (k >> 1)) * 32 + 2 * px + (k & 1)], s);
+                }
+                acc_w1[j] += s;
+            }
+        }
+        if (warp < C1) {
+            float s = 0.f;
+            for (int pp = lane; pp < 196; pp += 32) s += sG1[warp * 196 + pp];
+            s = warp_sum(s);
+            acc_b1 += s;
+        }
+    }
+
+    // ---- one partial row per CTA ----
+    float* row = a.partials + (long)blockIdx.x * a.partial_stride;
+#pragma unroll
+    for (int j = 0; j < C::W2_PER_THREAD; ++j) {
+        const int o = tid + j * CB_NT;
+        if (o < C::W2N) row[a.off_w2 + o] = acc_w2[j];
+    }
+#pragma unroll
+    for (int j = 0; j < C::W1_PER_THREAD; ++j) {
+        const int o = tid + j * CB_NT;
+        if (o < C::W1N) row[a.off_w1 + o] = acc_w1[j];
+    }
+    if (tid < C2) row[a.off_b2 + tid] = acc_b2;
+    if (warp < C1 && lane == 0) row[a.off_b1 + warp] = acc_b1;
+}
+
+static int num_partials_for(int B) {
+    int n = (B + 1) / 2;
+    if (n > CB_MAX_PARTIALS) n = CB_MAX_PARTIALS;
+    return n < 1 ? 1 : n;
+}
+
+}  // namespace b200dp
+
+using namespace b200dp;
+
+extern "C" int b200dp_conv_bwd_num_partials(b200dp_dims d) { return num_partials_for(d.batch); }
+
+extern "C" int b200dp_conv_bwd(const void* x, int in_is_u8, float mean, float std, const float* p1,
+                               const uint8_t* idx1, const float* p2, const uint8_t* idx2, const float* dp2,
+                               const float* w2, float* partials, int partial_stride, int off_w1, int off_b1,
+                               int off_w2, int off_b2, b200dp_dims d, b200dp_stream_t s) {
+    B200DP_REQUIRE(d.in_ch == 1 && d.c1 == 6 && d.c2 == 16,
+                   "the fused CUDA-core conv backward covers the reference LeNet (1,6,16); "
+                   "the wide model goes through the tensor-core kernels");
+    B200DP_REQUIRE(d.in_hw == 28 || d.in_hw == 32, "in_hw must be 28 or 32");
+    using C = ConvBwdCfg<1, 6, 16>;
+    B200DP_REQUIRE(off_w1 + C::W1N <= partial_stride && off_w2 + C::W2N <= partial_stride &&
+                   off_b1 + 6 <= partial_stride && off_b2 + 16 <= partial_stride, "partial row too short");
+    ConvBwdArgs a{x, in_is_u8, d.in_hw, mean, std, p1, idx1, p2, idx2, dp2, w2, partials, partial_stride,
+                  off_w1, off_b1, off_w2, off_b2, d.batch};
+    auto kern = conv_bwd_kernel<1, 6, 16>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        B200DP_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+        attr_done = true;
+    }
+    kern<<<num_partials_for(d.batch), CB_NT, C::SMEM, (cudaStream_t)s>>>(a);
+    B200DP_CHECK(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,147 @@
+/*
+ * b200dp — C ABI of the in-tree CUDA library (csrc/*.cu, built for sm_100a only).
+ *
+ * Every entry point is `extern "C"`, takes raw device pointers plus the CUDA
+ * stream to launch on, allocates nothing unless its name says so, and returns
+ * a cudaError_t-compatible int (0 = success).  Python binds these with ctypes
+ * (b200dp/ops/native.py); a C/C++ host program can link the .so directly.
+ *
+ * Each declaration cites the reference code it replaces (file:line in
+ * ownzonefeng/pytorch-distributed-training-example).
+ *
+ * Tensor layouts are PyTorch's: activations NCHW fp32, conv weights OIHW,
+ * linear weights (out,in), all contiguous.
+ */
+#ifndef B200DP_H_
+#define B200DP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b200dp_stream_t; /* cudaStream_t */
+
+/* Model geometry.  LeNet family: conv5(in_ch->c1)+pool, conv5(c1->c2)+pool,
+ * conv5(c2->c3) on a 5x5 map (== GEMM), fc(c3->f1), fc(f1->ncls).
+ * Supported: {in_ch=1,c1=6,c2=16} (reference cnn.py:9-23) and the 4x widened
+ * CIFAR-shaped {in_ch=3,c1=24,c2=64}; c3, f1 are free; ncls <= 16. */
+typedef struct {
+    int batch;
+    int in_ch;
+    int in_hw;   /* 28 (bilinear-upsampled to 32 on the fly) or 32 */
+    int c1, c2, c3, f1, ncls;
+} b200dp_dims;
+
+int b200dp_version(void);
+const char* b200dp_last_error(void);
+
+/* ---- forward -------------------------------------------------------------
+ * conv1 stage: [normalise (x/255-mean)/std when in_is_u8] -> bilinear 28->32
+ * (align_corners) -> conv5x5 + bias -> LeakyReLU(0.2) -> maxpool 2x2 (+argmax).
+ * Replaces train.py:85 (transform), cnn.py:9-12.   x: [B][in_ch][hw][hw] u8|f32,
+ * out p1: [B][c1][14][14], idx1 (nullable): uint8 argmax 0..3 per pooled cell. */
+int b200dp_conv1_fwd(const void* x, int in_is_u8, float mean, float std, const float* w, const float* b,
+                     float* p1, uint8_t* idx1, b200dp_dims d, b200dp_stream_t s);
+
+/* conv2 stage: conv5x5 + bias -> LeakyReLU -> maxpool (+argmax).  cnn.py:13-15.
+ * p1: [B][c1][14][14] -> p2: [B][c2][5][5] */
+int b200dp_conv2_fwd(const float* p1, const float* w, const float* b, float* p2, uint8_t* idx2,
+                     b200dp_dims d, b200dp_stream_t s);
+
+/* Dense layer y = act(x W^T + b) on CUDA cores; act: 0 none, 1 LeakyReLU(0.2).
+ * conv3 (cnn.py:16-17, a GEMM because the map is 5x5) and FC.0 (cnn.py:20-21). */
+int b200dp_linear_fwd(const float* x, const float* w, const float* b, float* y, int M, int N, int K, int act,
+                      b200dp_stream_t s);
+
+/* Head tail, one warp per row: logits = h1 W^T + b -> softmax -> loss -> dlogits
+ * -> dz1 = (dlogits W) * leaky'(h1).   cnn.py:22-23 + train.py:48 (+ backward).
+ * loss_mode 0 = "ref": nll_loss on probabilities, L = -mean p[target];
+ *           1 = "xent": cross-entropy.
+ * loss_out[0] = batch mean loss (deterministic fixed-order sum).
+ * eval_acc (nullable): [0] += sum-reduced loss, [1] += #correct (double[2]) —
+ * the eval loop of train.py:60-72 without per-batch host syncs.
+ * dlogits/dz1 may be null in eval mode.  ticket: int[1] zero-initialised scratch. */
+int b200dp_head_tail(const float* h1, const float* w, const float* b, const int64_t* target, int loss_mode,
+                     float* probs, float* loss_rows, float* loss_out, float* dlogits, float* dz1,
+                     double* eval_acc, int* ticket, int B, int F1, int ncls, b200dp_stream_t s);
+
+/* ---- backward ------------------------------------------------------------
+ * Up to four independent GEMM-shaped backward problems in ONE launch.
+ * kind 0: dX[M][K] = (dY[M][N] W[N][K]) * leaky'(act_prev[M][K])   (act_prev nullable)
+ * kind 1: dW[N][K] = dY[M][N]^T X[M][K],  db[N] = colsum(dY)       (db nullable)
+ * Replaces the autograd backward of cnn.py:16-22 (train.py:49). */
+typedef struct {
+    int kind;
+    const float* dy; const float* w_or_x; const float* act_prev;
+    float* out; float* db;
+    int M, N, K;
+} b200dp_bwd_problem;
+int b200dp_linear_bwd_group(const b200dp_bwd_problem* probs, int count, b200dp_stream_t s);
+
+/* Fused convolution backward for one step: pool2-bwd + leaky-bwd + conv2 dgrad
+ * + conv2 wgrad/bgrad + pool1-bwd + leaky-bwd + conv1 wgrad/bgrad (no conv1
+ * dgrad: the input needs no gradient).   train.py:49 / cnn.py:9-15.
+ * Covers the reference geometry (in_ch=1, c1=6, c2=16).  A CTA owns images cta, cta+grid, ...
+ * and writes ONE row of the scratch buffer `partials` ([n_partials][partial_stride] floats,
+ * n_partials = b200dp_conv_bwd_num_partials(d)); within a row the four gradients sit at the
+ * column offsets off_w1/off_b1/off_w2/off_b2 (the arena layout of the conv bucket, so a row can
+ * be summed straight into the gradient arena).  Columns the kernel does not own are never
+ * written: allocate the buffer zeroed.  Rows are summed in fixed order by b200dp_reduce_update
+ * (deterministic; no atomics). */
+int b200dp_conv_bwd_num_partials(b200dp_dims d);
+int b200dp_conv_bwd(const void* x, int in_is_u8, float mean, float std, const float* p1, const uint8_t* idx1,
+                    const float* p2, const uint8_t* idx2, const float* dp2, const float* w2, float* partials,
+                    int partial_stride, int off_w1, int off_b1, int off_w2, int off_b2,
+                    b200dp_dims d, b200dp_stream_t s);
+
+/* ---- gradient reduction + optimizer update (the product kernel) -----------
+ * One launch per bucket [start, start+count) of the flat arenas:
+ *   1. (optional) sum `n_partials` partial-gradient rows into grad[]
+ *   2. (world > 1) publish the bucket into this rank's symmetric staging
+ *      buffer, signal per-slice flags in every peer, wait for the peers'
+ *      flags, read every rank's slice over NVLink (P2P loads) and sum in rank
+ *      order — identical result on all ranks
+ *   3. scale by 1/world, apply Adadelta / SGD-momentum / Adam to param[] and
+ *      the state arenas (fp32), optionally write bf16 shadow weights.
+ * Replaces train.py:34-39 (10x all_reduce + divide) and train.py:51
+ * (optimizer.step), and train.py:46 (zero_grad: nothing accumulates).
+ *
+ * partials (nullable): [n_partials][partial_stride] rows whose column i is arena element start+i.
+ * hyper (device, float[8]): {lr, h0, h1, h2, weight_decay, -, -, -}; Adadelta h0=rho h1=eps,
+ * SGD h0=momentum h1=nesterov, Adam h0=beta1 h1=beta2 h2=eps (bias correction is computed on the
+ * device from the generation number).  Read on the device so a captured CUDA graph sees
+ * scheduler changes.
+ * step_counter (device, uint32[4], zero-initialised): [0] generation (= optimizer steps done),
+ * [1] ticket, [2] error flag (1 = a peer did not answer within the spin bound).  The LAST
+ * bucket launch of a step (last_bucket != 0) advances the generation. */
+typedef struct {
+    int world, rank;
+    int algo;                 /* 0 one-shot, 1 two-shot, 2 NVLS multimem */
+    float* stage[8];          /* every rank's staging base (peer-mapped), [2 parities][arena_len] */
+    uint32_t* flags[8];       /* every rank's flag block (peer-mapped) */
+    float* mc_stage;          /* multicast alias of stage (NVLS) or NULL */
+    int arena_len;            /* floats per parity buffer */
+    int max_slices;           /* flag slots per source rank */
+} b200dp_comm;
+
+int b200dp_reduce_update(float* param, float* grad, float* state0, float* state1, uint16_t* shadow_bf16,
+                         int start, int count, const float* partials, int n_partials, int partial_stride,
+                         int opt_kind, const float* hyper, uint32_t* step_counter, int last_bucket,
+                         const b200dp_comm* comm, b200dp_stream_t s);
+
+/* ---- symmetric memory plumbing (replaces the NCCL communicator of train.py:26-31) ----
+ * Allocation of peer-mappable device memory and exchange via CUDA IPC handles
+ * (64 opaque bytes each, shipped between ranks by torch.distributed at start-up). */
+int b200dp_symm_alloc(void** ptr, uint64_t bytes);           /* cudaMalloc + zero */
+int b200dp_symm_free(void* ptr);
+int b200dp_symm_export(void* ptr, uint8_t handle_out[64]);
+int b200dp_symm_import(const uint8_t handle[64], void** ptr_out);
+int b200dp_symm_close(void* imported_ptr);
+int b200dp_enable_peer_access(int peer_device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DP_H_ */
