@@ -71,7 +71,8 @@ class NativeLeNet:
         self.dp2 = torch.empty(B, c.c2 * 25, **f32)
         self.ticket = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.eval_acc = torch.zeros(2, dtype=torch.float64, device=self.device)
-        self.n_partials = native.conv_bwd_num_partials(self.dims(B))
+        self.n_partials = native.conv_bwd_num_partials(self.dims(B))   # rows allocated (full batch)
+        self.cur_partials = self.n_partials    # rows the last backward actually wrote (fewer on a ragged batch)
         self.partial_stride = self.bucket_conv.numel
         # scratch: one partial-gradient row per conv-backward CTA (zeroed once: padding columns stay 0)
         self.partials = torch.zeros(self.n_partials, self.partial_stride, **f32)
@@ -120,6 +121,7 @@ class NativeLeNet:
         if on_bucket:
             on_bucket(1)
         ow1, ob1, ow2, ob2 = self.conv_offsets
+        self.cur_partials = native.conv_bwd_num_partials(d)
         native.conv_bwd(x, self.spec.mean, self.spec.std, self.p1, self.idx1, self.p2, self.idx2, self.dp2,
                         w["ConvNet.4.weight"], self.partials, self.partial_stride, ow1, ob1, ow2, ob2, d)
         if on_bucket:
@@ -175,7 +177,7 @@ class NativeStepper:
         b = self.arena.layout.buckets[bucket_index]
         is_conv = bucket_index == 2
         native.reduce_update(self.arena.param, self.arena.grad, opt.state0, opt.state1, None, b.start, b.numel,
-                             net.partials if is_conv else None, net.n_partials if is_conv else 0,
+                             net.partials if is_conv else None, net.cur_partials if is_conv else 0,
                              net.partial_stride if is_conv else 0, opt.hyper.code(), self.hyper_dev,
                              self.step_counter, bucket_index == 2, self.comm.struct if self.comm else None)
 
