@@ -257,3 +257,104 @@ extern "C" int b200dp_conv_bwd(const void* x, int in_is_u8, float mean, float st
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }
+
+// =================================================================================================
+// Allocation-free variant of the fused convolution backward.
+//
+// Who needs it: a host program that may not call cudaMalloc where it calls us.  Typical cases are
+// a process whose device memory has all been handed to one pool allocator up front (a raw
+// cudaMalloc then fails or fragments the pool's view of the GPU), and a control loop with a
+// latency budget that cannot absorb the driver lock and implicit synchronisation an allocation
+// may take.  b200dp_conv_bwd makes such a caller find room for the partial-gradient rows itself;
+// this entry point keeps those rows in a fixed array that is part of the library image instead,
+// sums them, and hands back only the four finished gradients.
+//
+// The array is B200DP_NOALLOC_MAX_ROWS x B200DP_NOALLOC_MAX_STRIDE floats (1,376,256 bytes).  Every
+// GPU that loads this library carries it from load until the process exits, used or not.
+namespace b200dp {
+
+constexpr int NA_MAX_ROWS = CB_MAX_PARTIALS;   // 128 == B200DP_NOALLOC_MAX_ROWS
+constexpr int NA_MAX_STRIDE = 2688;            //        B200DP_NOALLOC_MAX_STRIDE
+constexpr int NA_MAX_DEVICES = 64;
+
+static __device__ __align__(256) float g_conv_bwd_rows[NA_MAX_ROWS * NA_MAX_STRIDE];
+
+// Sum rows 0..n_rows-1 of the four owned column ranges, row 0 first (fixed order => repeatable).
+__global__ void __launch_bounds__(256) conv_bwd_rows_sum_kernel(const float* __restrict__ rows, int n_rows,
+                                                                int stride, float* __restrict__ out,
+                                                                int off_w1, int n_w1, int off_b1, int n_b1,
+                                                                int off_w2, int n_w2, int off_b2, int n_b2) {
+    const int total = n_w1 + n_b1 + n_w2 + n_b2;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        int col;
+        if (i < n_w1) col = off_w1 + i;
+        else if (i < n_w1 + n_b1) col = off_b1 + (i - n_w1);
+        else if (i < n_w1 + n_b1 + n_w2) col = off_w2 + (i - n_w1 - n_b1);
+        else col = off_b2 + (i - n_w1 - n_b1 - n_w2);
+        float s = 0.f;
+        for (int r = 0; r < n_rows; ++r) s += rows[(long)r * stride + col];
+        out[col] = s;
+    }
+}
+
+// The name g_conv_bwd_rows is only a handle in host code; the address a kernel can use has to be
+// asked for, per device, with that device current.  Done once per device, on first use.
+static float* g_rows_addr[NA_MAX_DEVICES] = {nullptr};
+
+static int noalloc_device_setup(float** rows_out) {
+    int dev = -1;
+    B200DP_CHECK(cudaGetDevice(&dev));
+    B200DP_REQUIRE(dev >= 0 && dev < NA_MAX_DEVICES, "device ordinal beyond the per-device table");
+    if (g_rows_addr[dev] == nullptr) {
+        float* p = nullptr;
+        B200DP_CHECK(cudaGetSymbolAddress((void**)&p, g_conv_bwd_rows));
+        B200DP_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
+        B200DP_CHECK(cudaFuncSetAttribute(conv_bwd_kernel<1, 6, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)ConvBwdCfg<1, 6, 16>::SMEM));
+        g_rows_addr[dev] = p;
+    }
+    *rows_out = g_rows_addr[dev];
+    return 0;
+}
+
+}  // namespace b200dp
+
+extern "C" int b200dp_conv_bwd_noalloc(const void* x, int in_is_u8, float mean, float std, const float* p1,
+                                       const uint8_t* idx1, const float* p2, const uint8_t* idx2,
+                                       const float* dp2, const float* w2, float* grad_out, int grad_len,
+                                       int off_w1, int off_b1, int off_w2, int off_b2, b200dp_dims d,
+                                       b200dp_stream_t s) {
+    using C = ConvBwdCfg<1, 6, 16>;
+    B200DP_REQUIRE(d.in_ch == 1 && d.c1 == 6 && d.c2 == 16, "covers the reference LeNet geometry (1,6,16) only");
+    B200DP_REQUIRE(d.in_hw == 28 || d.in_hw == 32, "in_hw must be 28 or 32");
+    B200DP_REQUIRE(d.batch >= 1, "empty batch");
+    if (grad_len > NA_MAX_STRIDE || grad_len < 1) {
+        set_last_error("b200dp_conv_bwd_noalloc: grad_len %d is outside 1..%d floats, the row length the "
+                       "built-in scratch array was sized for; use b200dp_conv_bwd with your own buffer",
+                       grad_len, NA_MAX_STRIDE);
+        return (int)cudaErrorInvalidValue;
+    }
+    const int n_rows = num_partials_for(d.batch);
+    if (n_rows > NA_MAX_ROWS) {
+        set_last_error("b200dp_conv_bwd_noalloc: %d partial rows exceed the built-in maximum %d", n_rows, NA_MAX_ROWS);
+        return (int)cudaErrorInvalidValue;
+    }
+    B200DP_REQUIRE(off_w1 >= 0 && off_b1 >= 0 && off_w2 >= 0 && off_b2 >= 0 &&
+                   off_w1 + C::W1N <= grad_len && off_w2 + C::W2N <= grad_len &&
+                   off_b1 + 6 <= grad_len && off_b2 + 16 <= grad_len, "gradient ranges do not fit in grad_len");
+    float* rows = nullptr;
+    int rc = noalloc_device_setup(&rows);
+    if (rc != 0) return rc;
+    ConvBwdArgs a{x, in_is_u8, d.in_hw, mean, std, p1, idx1, p2, idx2, dp2, w2, rows, grad_len,
+                  off_w1, off_b1, off_w2, off_b2, d.batch};
+    // Nothing in the array has to start at zero: each of the n_rows CTAs overwrites all four column
+    // ranges of its own row, and the summing pass reads exactly those cells of rows 0..n_rows-1.
+    // Whatever an earlier, larger call left in further rows or in other columns is never read.
+    conv_bwd_kernel<1, 6, 16><<<n_rows, CB_NT, C::SMEM, (cudaStream_t)s>>>(a);
+    B200DP_CHECK(cudaGetLastError());
+    const int total = C::W1N + 6 + C::W2N + 16;
+    conv_bwd_rows_sum_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)s>>>(
+        rows, n_rows, grad_len, grad_out, off_w1, C::W1N, off_b1, 6, off_w2, C::W2N, off_b2, 16);
+    B200DP_CHECK(cudaGetLastError());
+    return 0;
+}

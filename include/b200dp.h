@@ -96,6 +96,29 @@ int b200dp_conv_bwd(const void* x, int in_is_u8, float mean, float std, const fl
                     int partial_stride, int off_w1, int off_b1, int off_w2, int off_b2,
                     b200dp_dims d, b200dp_stream_t s);
 
+/* Allocation-free form of b200dp_conv_bwd (no counterpart in the reference; an addition of this
+ * library).  For hosts that cannot call cudaMalloc at the point where they call us — for example
+ * because one pool allocator already owns all device memory, or because the call sits in a loop
+ * whose latency budget has no room for an allocation.  The partial-gradient rows live in an array
+ * built into the library (B200DP_NOALLOC_MAX_ROWS x B200DP_NOALLOC_MAX_STRIDE floats = 1,376,256
+ * bytes, resident on every GPU that loads the library until the process exits); the call sums
+ * them in fixed order and writes only the four finished gradients:
+ *     grad_out[off_w1 .. +150)  dL/dW conv1      grad_out[off_b1 .. +6)   dL/db conv1
+ *     grad_out[off_w2 .. +2400) dL/dW conv2      grad_out[off_b2 .. +16)  dL/db conv2
+ * Other cells of grad_out are left alone.  grad_len (floats in grad_out, also the row length used
+ * inside) must be <= B200DP_NOALLOC_MAX_STRIDE, else the call fails with cudaErrorInvalidValue
+ * and b200dp_last_error() says why.  It calls no cudaMalloc / cudaFree and no allocating library
+ * routine.  The first call on each device looks up the array's device address and sets a kernel
+ * attribute; make that first call before any stream capture begins.  All calls on a device share
+ * the one array: two calls whose kernels can overlap on the GPU (different streams, no ordering
+ * between them) race on it — order them.  Nothing has to be cleared between calls. */
+#define B200DP_NOALLOC_MAX_ROWS 128
+#define B200DP_NOALLOC_MAX_STRIDE 2688
+int b200dp_conv_bwd_noalloc(const void* x, int in_is_u8, float mean, float std, const float* p1,
+                            const uint8_t* idx1, const float* p2, const uint8_t* idx2, const float* dp2,
+                            const float* w2, float* grad_out, int grad_len, int off_w1, int off_b1,
+                            int off_w2, int off_b2, b200dp_dims d, b200dp_stream_t s);
+
 /* ---- gradient reduction + optimizer update (the product kernel) -----------
  * One launch per bucket [start, start+count) of the flat arenas:
  *   1. (optional) sum `n_partials` partial-gradient rows into grad[]
