@@ -70,7 +70,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             os.remove(o)
     with ThreadPoolExecutor(max_workers=8) as ex:
         objs = list(ex.map(lambda s: _compile(s, log_dir), sources()))
-    cmd = [_nvcc(), *ARCH, "-shared", "-o", LIB + ".tmp", *objs, "-lcuda"]
+    cmd = [_nvcc(), *ARCH, "-shared", "-o", LIB + ".tmp", *objs]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stderr[-4000:]}")

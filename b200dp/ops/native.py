@@ -28,6 +28,16 @@ class BwdProblem(C.Structure):
                 ("out", C.c_void_p), ("db", C.c_void_p), ("M", C.c_int), ("N", C.c_int), ("K", C.c_int)]
 
 
+class TcProblem(C.Structure):
+    _fields_ = [("a", C.c_void_p), ("lda", C.c_int), ("a_mn_major", C.c_int),
+                ("b", C.c_void_p), ("ldb", C.c_int), ("b_mn_major", C.c_int),
+                ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
+                ("bias", C.c_void_p), ("act", C.c_int),
+                ("mask", C.c_void_p), ("ld_mask", C.c_int),
+                ("out", C.c_void_p), ("ld_out", C.c_int),
+                ("colext", C.c_void_p)]
+
+
 class Comm(C.Structure):
     _fields_ = [("world", C.c_int), ("rank", C.c_int), ("algo", C.c_int),
                 ("stage", C.c_void_p * 8), ("flags", C.c_void_p * 8), ("mc_stage", C.c_void_p),
@@ -60,6 +70,7 @@ def load(build_if_missing: bool = True):
     lib.b200dp_linear_fwd.argtypes = [vp, vp, vp, vp, i, i, i, i, vp]
     lib.b200dp_head_tail.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
     lib.b200dp_linear_bwd_group.argtypes = [C.POINTER(BwdProblem), i, vp]
+    lib.b200dp_tc_gemm_group.argtypes = [C.POINTER(TcProblem), i, vp]
     lib.b200dp_conv_bwd_num_partials.argtypes = [Dims]
     lib.b200dp_conv_bwd.argtypes = [vp, i, f, f, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, Dims, vp]
     lib.b200dp_reduce_update.argtypes = [vp, vp, vp, vp, vp, i, i, vp, i, i, i, vp, vp, i, C.POINTER(Comm), vp]
@@ -136,6 +147,18 @@ def bwd_problem(kind: int, dy, w_or_x, act_prev, out, db, M: int, N: int, K: int
 def linear_bwd_group(problems: Sequence[BwdProblem]) -> None:
     arr = (BwdProblem * len(problems))(*problems)
     check(load().b200dp_linear_bwd_group(arr, len(problems), _stream()), "linear_bwd_group")
+
+
+def tc_problem(a, lda: int, a_mn: bool, b, ldb: int, b_mn: bool, M: int, N: int, K: int, *, bias=None, act: int = 0,
+               mask=None, ld_mask: int = 0, out=None, ld_out: int = 0, colext=None) -> TcProblem:
+    """One tensor-core GEMM problem: out[M][N] = epi(sum_k A(m,k) B(n,k)); see include/b200dp.h."""
+    return TcProblem(_p(a), lda, int(a_mn), _p(b), ldb, int(b_mn), M, N, K, _p(bias), act, _p(mask), ld_mask,
+                     _p(out), ld_out, _p(colext))
+
+
+def tc_gemm_group(problems: Sequence[TcProblem]) -> None:
+    arr = (TcProblem * len(problems))(*problems)
+    check(load().b200dp_tc_gemm_group(arr, len(problems), _stream()), "tc_gemm_group")
 
 
 def conv_bwd_num_partials(dims: Dims) -> int:

@@ -80,6 +80,28 @@ typedef struct {
 } b200dp_bwd_problem;
 int b200dp_linear_bwd_group(const b200dp_bwd_problem* probs, int count, b200dp_stream_t s);
 
+/* Tensor-core GEMMs (tcgen05.mma kind::tf32, TMEM accumulators, TMA-fed), up to four problems
+ * per launch, directly on fp32 tensors:  C[M][N] = epi( sum_k A(m,k) B(n,k) ).
+ * An operand is K-major when its memory is [MN rows][K cols] and MN-major when it is
+ * [K rows][MN cols] (lda/ldb = row pitch in floats, multiple of 4; base 16-byte aligned), so
+ *   y  = x W^T   : a = x (K-major),   b = W (K-major)
+ *   dX = dY W    : a = dY (K-major),  b = W (MN-major)
+ *   dW = dY^T X  : a = dY (MN-major), b = X (MN-major)
+ * need no transposed copies.  epi: + bias[n], LeakyReLU (act = 1), * LeakyReLU'(mask[m][n]).
+ * colext (nullable): logical column N-1 is written to colext[m] instead of out — with a column
+ * of ones in X this yields the bias gradient from the same GEMM.
+ * Replaces cnn.py:16-17, 20-22 and their backward (train.py:49); cuBLAS in the reference. */
+typedef struct {
+    const float* a; int lda; int a_mn_major;
+    const float* b; int ldb; int b_mn_major;
+    int M, N, K;
+    const float* bias; int act;
+    const float* mask; int ld_mask;
+    float* out; int ld_out;
+    float* colext;
+} b200dp_tc_problem;
+int b200dp_tc_gemm_group(const b200dp_tc_problem* probs, int count, b200dp_stream_t s);
+
 /* Fused convolution backward for one step: pool2-bwd + leaky-bwd + conv2 dgrad
  * + conv2 wgrad/bgrad + pool1-bwd + leaky-bwd + conv1 wgrad/bgrad (no conv1
  * dgrad: the input needs no gradient).   train.py:49 / cnn.py:9-15.
