@@ -41,9 +41,14 @@ class NativeLeNet:
     """Buffers + kernel launch sequences for one model replica on one GPU."""
 
     def __init__(self, cfg: LeNetConfig, batch: int, device: torch.device, *, loss_mode: str = "ref",
-                 spec: ImageSpec = MNIST_SPEC, module: Optional[LeNet] = None):
+                 spec: ImageSpec = MNIST_SPEC, module: Optional[LeNet] = None, tc: bool = False):
+        """``tc=True`` routes the five GEMM-shaped layers (conv3, FC.0 and their backward, FC.2's weight
+        gradient) through the tcgen05/TMEM/TMA tf32 kernel; ``tc=False`` keeps everything in exact fp32
+        on CUDA cores.  In tc mode the GEMM operand buffers carry one extra column of ones (the bias
+        gradients fall out of the weight-gradient GEMMs) and are padded to a 16-byte row pitch for TMA."""
         native.load()
         self.cfg, self.B, self.device, self.spec = cfg, int(batch), torch.device(device), spec
+        self.tc = bool(tc)
         self.loss_mode = _LOSS_MODES[loss_mode]
         self.module = module if module is not None else LeNet(cfg)
         self.module.to(self.device)
@@ -58,14 +63,27 @@ class NativeLeNet:
         u8 = dict(dtype=torch.uint8, device=self.device)
         self.p1 = torch.empty(B, c.c1, 14, 14, **f32)
         self.idx1 = torch.empty(B, c.c1, 14, 14, **u8)
-        self.p2 = torch.empty(B, c.c2, 5, 5, **f32)
+        k3 = c.c2 * 25
+        if self.tc:
+            self.ld_p2, self.ld_a3, self.ld_h1 = k3 + 4, c.c3 + 4, c.f1 + 4
+            self.ld_dl = (c.num_classes + 3) // 4 * 4
+            self.p2 = torch.zeros(B, self.ld_p2, **f32)
+            self.a3 = torch.zeros(B, self.ld_a3, **f32)
+            self.h1 = torch.zeros(B, self.ld_h1, **f32)
+            self.p2[:, k3] = 1.0            # ones columns: dW GEMMs then also produce db
+            self.a3[:, c.c3] = 1.0
+            self.h1[:, c.f1] = 1.0
+            self.dlogits = torch.zeros(B, self.ld_dl, **f32)
+        else:
+            self.ld_p2, self.ld_a3, self.ld_h1, self.ld_dl = 0, 0, 0, 0
+            self.p2 = torch.empty(B, c.c2, 5, 5, **f32)
+            self.a3 = torch.empty(B, c.c3, **f32)
+            self.h1 = torch.empty(B, c.f1, **f32)
+            self.dlogits = torch.empty(B, c.num_classes, **f32)
         self.idx2 = torch.empty(B, c.c2, 5, 5, **u8)
-        self.a3 = torch.empty(B, c.c3, **f32)
-        self.h1 = torch.empty(B, c.f1, **f32)
         self.probs = torch.empty(B, c.num_classes, **f32)
         self.loss_rows = torch.empty(B, **f32)
         self.loss = torch.zeros(1, **f32)
-        self.dlogits = torch.empty(B, c.num_classes, **f32)
         self.dz1 = torch.empty(B, c.f1, **f32)
         self.dz3 = torch.empty(B, c.c3, **f32)
         self.dp2 = torch.empty(B, c.c2 * 25, **f32)
@@ -84,7 +102,7 @@ class NativeLeNet:
 
     def dims(self, b: int) -> native.Dims:
         c = self.cfg
-        return native.Dims(b, c.in_ch, c.in_hw, c.c1, c.c2, c.c3, c.f1, c.num_classes)
+        return native.Dims(b, c.in_ch, c.in_hw, c.c1, c.c2, c.c3, c.f1, c.num_classes, self.ld_p2)
 
     # ---- forward ----------------------------------------------------------------
     def forward(self, x: torch.Tensor, y: torch.Tensor, train: bool) -> None:
@@ -95,31 +113,66 @@ class NativeLeNet:
                          d, self.spec.mean, self.spec.std)
         native.conv2_fwd(self.p1, w["ConvNet.4.weight"], w["ConvNet.4.bias"], self.p2,
                          self.idx2 if train else None, d)
-        native.linear_fwd(self.p2[:b].view(b, -1), w["ConvNet.7.weight"].view(self.cfg.c3, -1),
-                          w["ConvNet.7.bias"], self.a3[:b], 1)
-        native.linear_fwd(self.a3[:b], w["FC.0.weight"], w["FC.0.bias"], self.h1[:b], 1)
+        c = self.cfg
+        k3 = c.c2 * 25
+        if self.tc:
+            T = native.tc_problem
+            native.tc_gemm_group([T(self.p2, self.ld_p2, False, w["ConvNet.7.weight"], k3, False, b, c.c3, k3,
+                                    bias=w["ConvNet.7.bias"], act=1, out=self.a3, ld_out=self.ld_a3)])
+            native.tc_gemm_group([T(self.a3, self.ld_a3, False, w["FC.0.weight"], c.c3, False, b, c.f1, c.c3,
+                                    bias=w["FC.0.bias"], act=1, out=self.h1, ld_out=self.ld_h1)])
+        else:
+            native.linear_fwd(self.p2[:b].view(b, -1), w["ConvNet.7.weight"].view(c.c3, -1),
+                              w["ConvNet.7.bias"], self.a3[:b], 1)
+            native.linear_fwd(self.a3[:b], w["FC.0.weight"], w["FC.0.bias"], self.h1[:b], 1)
         native.head_tail(self.h1[:b], w["FC.2.weight"], w["FC.2.bias"], y, self.loss_mode, self.probs[:b],
                          self.loss_rows[:b], self.loss, self.dlogits[:b] if train else None,
-                         self.dz1[:b] if train else None, None if train else self.eval_acc, self.ticket)
+                         self.dz1[:b] if train else None, None if train else self.eval_acc, self.ticket,
+                         self.ld_h1, self.ld_dl)
 
     # ---- backward, in three launches; a callback fires as each bucket's gradients complete ----
     def backward(self, x: torch.Tensor, on_bucket=None) -> None:
         b, c, w, g = x.shape[0], self.cfg, self.w, self.g
         d = self.dims(b)
         k3 = c.c2 * 25
-        native.linear_bwd_group([
-            native.bwd_problem(1, self.dlogits, self.h1, None, g["FC.2.weight"], g["FC.2.bias"], b, c.num_classes, c.f1),
-            native.bwd_problem(1, self.dz1, self.a3, None, g["FC.0.weight"], g["FC.0.bias"], b, c.f1, c.c3),
-            native.bwd_problem(0, self.dz1, w["FC.0.weight"], self.a3, self.dz3, None, b, c.f1, c.c3),
-        ])
-        if on_bucket:
-            on_bucket(0)
-        native.linear_bwd_group([
-            native.bwd_problem(1, self.dz3, self.p2, None, g["ConvNet.7.weight"], g["ConvNet.7.bias"], b, c.c3, k3),
-            native.bwd_problem(0, self.dz3, w["ConvNet.7.weight"], None, self.dp2, None, b, c.c3, k3),
-        ])
-        if on_bucket:
-            on_bucket(1)
+        if self.tc:
+            T, nc = native.tc_problem, c.num_classes
+            native.tc_gemm_group([
+                # dW fc2 = dlogits^T h1 (+db through h1's ones column)
+                T(self.dlogits, self.ld_dl, True, self.h1, self.ld_h1, True, nc, c.f1 + 1, b,
+                  out=g["FC.2.weight"], ld_out=c.f1, colext=g["FC.2.bias"]),
+                # dW fc1 = dz1^T a3 (+db)
+                T(self.dz1, c.f1, True, self.a3, self.ld_a3, True, c.f1, c.c3 + 1, b,
+                  out=g["FC.0.weight"], ld_out=c.c3, colext=g["FC.0.bias"]),
+                # dz3 = (dz1 Wfc1) * leaky'(a3)
+                T(self.dz1, c.f1, False, w["FC.0.weight"], c.c3, True, b, c.c3, c.f1,
+                  mask=self.a3, ld_mask=self.ld_a3, out=self.dz3, ld_out=c.c3),
+            ])
+            if on_bucket:
+                on_bucket(0)
+            native.tc_gemm_group([
+                # dW conv3 = dz3^T p2 (+db)
+                T(self.dz3, c.c3, True, self.p2, self.ld_p2, True, c.c3, k3 + 1, b,
+                  out=g["ConvNet.7.weight"], ld_out=k3, colext=g["ConvNet.7.bias"]),
+                # dp2 = dz3 W3 (pool/activation masks are applied inside conv_bwd)
+                T(self.dz3, c.c3, False, w["ConvNet.7.weight"], k3, True, b, k3, c.c3, out=self.dp2, ld_out=k3),
+            ])
+            if on_bucket:
+                on_bucket(1)
+        else:
+            native.linear_bwd_group([
+                native.bwd_problem(1, self.dlogits, self.h1, None, g["FC.2.weight"], g["FC.2.bias"], b, c.num_classes, c.f1),
+                native.bwd_problem(1, self.dz1, self.a3, None, g["FC.0.weight"], g["FC.0.bias"], b, c.f1, c.c3),
+                native.bwd_problem(0, self.dz1, w["FC.0.weight"], self.a3, self.dz3, None, b, c.f1, c.c3),
+            ])
+            if on_bucket:
+                on_bucket(0)
+            native.linear_bwd_group([
+                native.bwd_problem(1, self.dz3, self.p2, None, g["ConvNet.7.weight"], g["ConvNet.7.bias"], b, c.c3, k3),
+                native.bwd_problem(0, self.dz3, w["ConvNet.7.weight"], None, self.dp2, None, b, c.c3, k3),
+            ])
+            if on_bucket:
+                on_bucket(1)
         ow1, ob1, ow2, ob2 = self.conv_offsets
         self.cur_partials = native.conv_bwd_num_partials(d)
         native.conv_bwd(x, self.spec.mean, self.spec.std, self.p1, self.idx1, self.p2, self.idx2, self.dp2,
@@ -137,10 +190,14 @@ class NativeStepper:
 
     def __init__(self, ctx, cfg: LeNetConfig, hyper: OptHyper, *, batch: int, loss_mode: str = "ref",
                  spec: ImageSpec = MNIST_SPEC, algo: str = "auto", graph: bool = True, overlap: bool = True,
-                 dtype: str = "bf16", module: Optional[LeNet] = None):
+                 dtype: str = "tf32", module: Optional[LeNet] = None):
         self.ctx, self.cfg = ctx, cfg
         self.device = ctx.device
-        self.net = NativeLeNet(cfg, batch, self.device, loss_mode=loss_mode, spec=spec, module=module)
+        if dtype not in ("fp32", "tf32", "bf16"):
+            raise ValueError(f"unknown dtype {dtype!r}")
+        self.dtype = "fp32" if dtype == "fp32" else "tf32"      # "bf16" is accepted as a request for the tensor-core path
+        self.net = NativeLeNet(cfg, batch, self.device, loss_mode=loss_mode, spec=spec, module=module,
+                               tc=self.dtype != "fp32")
         self.model = self.net.module
         self.arena = self.net.arena
         self.optimizer = FlatOptimizer(self.arena.param, self.arena.grad, hyper)

@@ -20,7 +20,7 @@ _lib = None
 
 class Dims(C.Structure):
     _fields_ = [("batch", C.c_int), ("in_ch", C.c_int), ("in_hw", C.c_int), ("c1", C.c_int),
-                ("c2", C.c_int), ("c3", C.c_int), ("f1", C.c_int), ("ncls", C.c_int)]
+                ("c2", C.c_int), ("c3", C.c_int), ("f1", C.c_int), ("ncls", C.c_int), ("ld_p2", C.c_int)]
 
 
 class BwdProblem(C.Structure):
@@ -68,7 +68,7 @@ def load(build_if_missing: bool = True):
     lib.b200dp_conv1_fwd.argtypes = [vp, i, f, f, vp, vp, vp, vp, Dims, vp]
     lib.b200dp_conv2_fwd.argtypes = [vp, vp, vp, vp, vp, Dims, vp]
     lib.b200dp_linear_fwd.argtypes = [vp, vp, vp, vp, i, i, i, i, vp]
-    lib.b200dp_head_tail.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
+    lib.b200dp_head_tail.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, vp]
     lib.b200dp_linear_bwd_group.argtypes = [C.POINTER(BwdProblem), i, vp]
     lib.b200dp_tc_gemm_group.argtypes = [C.POINTER(TcProblem), i, vp]
     lib.b200dp_conv_bwd_num_partials.argtypes = [Dims]
@@ -131,12 +131,13 @@ def linear_fwd(x, w, b, y, act: int) -> None:
     check(load().b200dp_linear_fwd(_p(x), _p(w), _p(b), _p(y), M, N, K, act, _stream()), "linear_fwd")
 
 
-def head_tail(h1, w, b, target, loss_mode: int, probs, loss_rows, loss_out, dlogits, dz1, eval_acc, ticket) -> None:
-    _f32(h1, w, b, probs, loss_rows, loss_out, dlogits, dz1)
-    B, F1 = h1.shape
+def head_tail(h1, w, b, target, loss_mode: int, probs, loss_rows, loss_out, dlogits, dz1, eval_acc, ticket,
+              ld_h1: int = 0, ld_dlogits: int = 0) -> None:
+    """``h1`` is [B][ld_h1] (ld 0 = dense F1 columns); F1 is taken from ``w``."""
+    B, F1 = h1.shape[0], w.shape[1]
     check(load().b200dp_head_tail(_p(h1), _p(w), _p(b), _p(target), loss_mode, _p(probs), _p(loss_rows),
                                   _p(loss_out), _p(dlogits), _p(dz1), _p(eval_acc), _p(ticket), B, F1,
-                                  w.shape[0], _stream()), "head_tail")
+                                  w.shape[0], ld_h1, ld_dlogits, _stream()), "head_tail")
 
 
 # ---- backward ----------------------------------------------------------------

@@ -52,6 +52,8 @@ def _parse():
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--no-overlap", action="store_true")
     p.add_argument("--input", choices=["u8", "f32"], default="u8", help="host->device input format (e2e)")
+    p.add_argument("--dtype", choices=["fp32", "tf32"], default="tf32",
+                   help="tf32 = tcgen05 tensor-core GEMMs on fp32 tensors; fp32 = exact CUDA-core kernels")
     return p.parse_args()
 
 
@@ -109,7 +111,7 @@ def run_own(args):
     torch.manual_seed(5)
     stepper = NativeStepper(ctx, cfg, OptHyper(args.optimizer, lr=0.1 if args.optimizer == "adadelta" else 0.01),
                             batch=batch, loss_mode="ref", spec=spec, graph=not args.no_graph,
-                            overlap=not args.no_overlap)
+                            overlap=not args.no_overlap, dtype=args.dtype)
     K, W = args.steps, args.warmup
 
     # ---- device-resident input pool larger than L2, cycled (timing rule) ----
@@ -182,7 +184,9 @@ def run_own(args):
             "value": imgs / (ms / 1e3), "unit": "images/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True,
             "scaling": "strong" if args.config == "strong4096" else "weak",
-            "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": "b200dp",
+            "vs_baseline": None,
+            "dtype": "tf32 tensor-core GEMMs (fp32 storage/accumulate), fp32 convs" if args.dtype == "tf32" else "fp32",
+            "data": "synthetic", "impl": "b200dp",
             "config": {"model": "cnn.py LeNet" if args.config != "wide_cifar" else "cnn.py LeNet 4x wide, CIFAR-shaped",
                        "global_batch": batch * world, "per_gpu_batch": batch, "seq_len": None,
                        "input": f"{spec.channels}x{spec.height}x{spec.width}",

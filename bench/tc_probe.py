@@ -1,0 +1,29 @@
+"""Where does the time go inside one tcgen05 GEMM CTA?  Prints clock64 deltas (cycles)."""
+import ctypes as C
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from b200dp.ops import native
+
+lib = native.load()
+lib.b200dp_tc_gemm_group_timed.argtypes = [C.POINTER(native.TcProblem), C.c_int, C.c_void_p, C.c_void_p]
+dev = "cuda"
+for (M, N, K, amn, bmn) in [(256, 120, 400, False, False), (256, 84, 120, False, False), (120, 401, 256, True, True),
+                            (256, 400, 120, False, True)]:
+    a = torch.randn((K, M + 4) if amn else (M, K + 4), device=dev)
+    b = torch.randn((K, (N + 3) // 4 * 4) if bmn else (N, K + 4), device=dev)
+    out = torch.empty(M, N, device=dev)
+    bias = torch.randn(N, device=dev)
+    dbg = torch.zeros(32, dtype=torch.int64, device=dev)
+    prob = native.tc_problem(a, a.shape[1], amn, b, b.shape[1], bmn, M, N, K, bias=bias, act=1, out=out, ld_out=N)
+    arr = (native.TcProblem * 1)(prob)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for it in range(3):
+        e0.record()
+        rc = lib.b200dp_tc_gemm_group_timed(arr, 1, dbg.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        e1.record()
+        torch.cuda.synchronize()
+    t = dbg.tolist()
+    t0 = t[0]
+    print(f"M{M} N{N} K{K} amn={amn} bmn={bmn}: event {e0.elapsed_time(e1)*1e3:.1f} us | setup {t[1]-t0} acc_done {t[2]-t0} "
+          f"epi_done {t[3]-t0} end {t[4]-t0} | issued {[x-t0 for x in t[8:16] if x]} | landed {[x-t0 for x in t[16:24] if x]}")

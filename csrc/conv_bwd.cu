@@ -21,7 +21,7 @@ constexpr int ZP = 18;  // 10x10 conv2-output map zero-padded by 4 on each side
 struct ConvBwdArgs {
     const void* x; int in_is_u8; int in_hw; float mean, std;
     const float* p1; const uint8_t* idx1;
-    const float* p2; const uint8_t* idx2; const float* dp2;
+    const float* p2; int ld_p2; const uint8_t* idx2; const float* dp2;
     const float* w2;
     float* partials; int partial_stride;
     int off_w1, off_b1, off_w2, off_b2;
@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(CB_NT) conv_bwd_kernel(ConvBwdArgs a) {
         for (int i = tid; i < C2 * 25; i += CB_NT) {
             const long o = (long)img * C2 * 25 + i;
             const int pp = i % 25, py = pp / 5, px = pp - py * 5, k = a.idx2[o];
-            sG2[i] = a.dp2[o] * leaky_grad_from_act(a.p2[o]);
+            sG2[i] = a.dp2[o] * leaky_grad_from_act(a.p2[(long)img * a.ld_p2 + i]);
             sPos2[i] = ((2 * py + (k >> 1)) << 8) | (2 * px + (k & 1));
         }
         for (int i = tid; i < C::F_DZ2; i += CB_NT) sdZ2[i] = 0.f;
@@ -245,7 +245,7 @@ extern "C" int b200dp_conv_bwd(const void* x, int in_is_u8, float mean, float st
     using C = ConvBwdCfg<1, 6, 16>;
     B200DP_REQUIRE(off_w1 + C::W1N <= partial_stride && off_w2 + C::W2N <= partial_stride &&
                    off_b1 + 6 <= partial_stride && off_b2 + 16 <= partial_stride, "partial row too short");
-    ConvBwdArgs a{x, in_is_u8, d.in_hw, mean, std, p1, idx1, p2, idx2, dp2, w2, partials, partial_stride,
+    ConvBwdArgs a{x, in_is_u8, d.in_hw, mean, std, p1, idx1, p2, d.ld_p2 > 0 ? d.ld_p2 : 400, idx2, dp2, w2, partials, partial_stride,
                   off_w1, off_b1, off_w2, off_b2, d.batch};
     auto kern = conv_bwd_kernel<1, 6, 16>;
     static bool attr_done = false;
@@ -345,7 +345,7 @@ extern "C" int b200dp_conv_bwd_noalloc(const void* x, int in_is_u8, float mean, 
     float* rows = nullptr;
     int rc = noalloc_device_setup(&rows);
     if (rc != 0) return rc;
-    ConvBwdArgs a{x, in_is_u8, d.in_hw, mean, std, p1, idx1, p2, idx2, dp2, w2, rows, grad_len,
+    ConvBwdArgs a{x, in_is_u8, d.in_hw, mean, std, p1, idx1, p2, d.ld_p2 > 0 ? d.ld_p2 : 400, idx2, dp2, w2, rows, grad_len,
                   off_w1, off_b1, off_w2, off_b2, d.batch};
     // Nothing in the array has to start at zero: each of the n_rows CTAs overwrites all four column
     // ranges of its own row, and the summing pass reads exactly those cells of rows 0..n_rows-1.

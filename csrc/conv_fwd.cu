@@ -31,6 +31,7 @@ struct ConvFwdArgs {
     uint8_t* idx;       // same shape, nullable
     int B, in_is_u8, in_hw;
     float mean, std;
+    int out_img_stride;  // floats between consecutive images of `out` (>= COUT*PP)
 };
 
 template <int CIN, int COUT, int IN_W, int OCT, int GPB, int IPB, bool FIRST>
@@ -128,7 +129,7 @@ conv5_pool_fwd_kernel(ConvFwdArgs a) {
             if (v > best) { best = v; bi = k; }
         }
         const long off = ((long)img * COUT + oc) * C::PP + pos;
-        a.out[off] = best;
+        a.out[(long)img * a.out_img_stride + oc * C::PP + pos] = best;
         if (a.idx) a.idx[off] = (uint8_t)bi;
     }
 }
@@ -156,7 +157,7 @@ using namespace b200dp;
 extern "C" int b200dp_conv1_fwd(const void* x, int in_is_u8, float mean, float std, const float* w, const float* b,
                                 float* p1, uint8_t* idx1, b200dp_dims d, b200dp_stream_t s) {
     B200DP_REQUIRE(d.in_hw == 28 || d.in_hw == 32, "in_hw must be 28 or 32");
-    ConvFwdArgs a{x, w, b, p1, idx1, d.batch, in_is_u8, d.in_hw, mean, std};
+    ConvFwdArgs a{x, w, b, p1, idx1, d.batch, in_is_u8, d.in_hw, mean, std, d.c1 * 196};
     if (d.in_ch == 1 && d.c1 == 6) return launch_conv_fwd<1, 6, 32, 3, 2, 1, true>(a, (cudaStream_t)s);
     if (d.in_ch == 3 && d.c1 == 24) return launch_conv_fwd<3, 24, 32, 4, 2, 1, true>(a, (cudaStream_t)s);
     B200DP_REQUIRE(false, "unsupported (in_ch, c1): expected (1,6) or (3,24)");
@@ -164,7 +165,8 @@ extern "C" int b200dp_conv1_fwd(const void* x, int in_is_u8, float mean, float s
 
 extern "C" int b200dp_conv2_fwd(const float* p1, const float* w, const float* b, float* p2, uint8_t* idx2,
                                 b200dp_dims d, b200dp_stream_t s) {
-    ConvFwdArgs a{p1, w, b, p2, idx2, d.batch, 0, 14, 0.f, 1.f};
+    ConvFwdArgs a{p1, w, b, p2, idx2, d.batch, 0, 14, 0.f, 1.f, d.ld_p2 > 0 ? d.ld_p2 : d.c2 * 25};
+    B200DP_REQUIRE(a.out_img_stride >= d.c2 * 25, "ld_p2 smaller than c2*25");
     if (d.c1 == 6 && d.c2 == 16) return launch_conv_fwd<6, 16, 14, 4, 4, 2, false>(a, (cudaStream_t)s);
     if (d.c1 == 24 && d.c2 == 64) return launch_conv_fwd<24, 64, 14, 4, 4, 2, false>(a, (cudaStream_t)s);
     B200DP_REQUIRE(false, "unsupported (c1, c2): expected (6,16) or (24,64)");

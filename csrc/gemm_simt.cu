@@ -63,11 +63,19 @@ __global__ void __launch_bounds__(GEMM_NT) gemm_group_kernel(GemmGroup g) {
     __shared__ float Red[KG][BM][BN + 1];
     __shared__ float RedCs[KG][BM];
 
+    // Select the problem with compile-time indices: a run-time index into the kernel parameter turns
+    // every field access into a slow indexed constant load inside the loops.
     int pi = 0;
-#pragma unroll
-    for (int i = 1; i < 4; ++i)
-        if (i < g.count && (int)blockIdx.x >= g.p[i].tile_start) pi = i;
-    const GemmProblem& p = g.p[pi];
+    if (g.count > 1 && (int)blockIdx.x >= g.p[1].tile_start) pi = 1;
+    if (g.count > 2 && (int)blockIdx.x >= g.p[2].tile_start) pi = 2;
+    if (g.count > 3 && (int)blockIdx.x >= g.p[3].tile_start) pi = 3;
+    GemmProblem p;
+    switch (pi) {
+        case 1: p = g.p[1]; break;
+        case 2: p = g.p[2]; break;
+        case 3: p = g.p[3]; break;
+        default: p = g.p[0]; break;
+    }
     const int tile = blockIdx.x - p.tile_start;
     const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
     const int m0 = tm * BM, n0 = tn * BN;

@@ -22,6 +22,7 @@ struct HeadTailArgs {
     float* probs; float* loss_rows; float* loss_out; float* dlogits; float* dz1;
     double* eval_acc; int* ticket;
     int B, F1, ncls, loss_mode;
+    int ld_h1, ld_dl;
 };
 
 __global__ void __launch_bounds__(HT_ROWS * 32) head_tail_kernel(HeadTailArgs a) {
@@ -39,7 +40,7 @@ __global__ void __launch_bounds__(HT_ROWS * 32) head_tail_kernel(HeadTailArgs a)
 #pragma unroll
         for (int j = 0; j < HT_MAXK; ++j) {
             int k = lane + 32 * j;
-            h[j] = (k < a.F1) ? a.h1[(long)row * a.F1 + k] : 0.f;
+            h[j] = (k < a.F1) ? a.h1[(long)row * a.ld_h1 + k] : 0.f;
         }
         float z[HT_MAXC];
 #pragma unroll
@@ -89,7 +90,7 @@ __global__ void __launch_bounds__(HT_ROWS * 32) head_tail_kernel(HeadTailArgs a)
                 float dv = 0.f;
 #pragma unroll
                 for (int c = 0; c < HT_MAXC; ++c) if (c == lane) dv = dz[c];
-                a.dlogits[(long)row * a.ncls + lane] = dv;
+                a.dlogits[(long)row * a.ld_dl + lane] = dv;
             }
             if (a.dz1) {
 #pragma unroll
@@ -115,32 +116,35 @@ __global__ void __launch_bounds__(HT_ROWS * 32) head_tail_kernel(HeadTailArgs a)
     __syncthreads();
     if (!sLast) return;
     __threadfence();
-    if (warp == 0) {
+    // all 256 threads of the last CTA: thread t sums rows t, t+256, ... ; warp butterflies; warp 0 adds the
+    // eight warp sums in order.  Fixed order => bit-reproducible; ~3 L2 round trips instead of B/32.
+    __shared__ float sSum[HT_ROWS];
+    __shared__ int sCnt[HT_ROWS];
+    float v = 0.f;
+    int ok = 0;
+    for (int r = tid; r < a.B; r += HT_ROWS * 32) {
+        v += __ldcg(a.loss_rows + r);
+        if (a.eval_acc) {
+            int am = 0; float bst = -INFINITY;
+            for (int c = 0; c < a.ncls; ++c) {
+                float pv = __ldcg(a.probs + (long)r * a.ncls + c);
+                if (pv > bst) { bst = pv; am = c; }
+            }
+            ok += (am == (int)a.target[r]);
+        }
+    }
+    v = warp_sum(v);
+    ok = __reduce_add_sync(0xffffffffu, ok);
+    if (lane == 0) { sSum[warp] = v; sCnt[warp] = ok; }
+    __syncthreads();
+    if (tid == 0) {
         float s = 0.f;
         int correct = 0;
-        for (int r0 = 0; r0 < a.B; r0 += 32) {
-            int r = r0 + lane;
-            float v = 0.f;
-            int ok = 0;
-            if (r < a.B) {
-                v = __ldcg(a.loss_rows + r);
-                if (a.eval_acc) {
-                    int am = 0; float bst = -INFINITY;
-                    for (int c = 0; c < a.ncls; ++c) {
-                        float pv = __ldcg(a.probs + (long)r * a.ncls + c);
-                        if (pv > bst) { bst = pv; am = c; }
-                    }
-                    ok = (am == (int)a.target[r]);
-                }
-            }
-            s += warp_sum(v);     // fixed order: 32-row blocks, butterfly inside
-            correct += __popc(__ballot_sync(0xffffffffu, ok));
-        }
-        if (lane == 0) {
-            a.loss_out[0] = s / (float)a.B;
-            if (a.eval_acc) { a.eval_acc[0] += (double)s; a.eval_acc[1] += (double)correct; }
-            *a.ticket = 0;   // re-arm for the next launch
-        }
+#pragma unroll
+        for (int w = 0; w < HT_ROWS; ++w) { s += sSum[w]; correct += sCnt[w]; }
+        a.loss_out[0] = s / (float)a.B;
+        if (a.eval_acc) { a.eval_acc[0] += (double)s; a.eval_acc[1] += (double)correct; }
+        *a.ticket = 0;   // re-arm for the next launch
     }
 }
 
@@ -150,13 +154,14 @@ using namespace b200dp;
 
 extern "C" int b200dp_head_tail(const float* h1, const float* w, const float* b, const int64_t* target,
                                 int loss_mode, float* probs, float* loss_rows, float* loss_out, float* dlogits,
-                                float* dz1, double* eval_acc, int* ticket, int B, int F1, int ncls,
-                                b200dp_stream_t s) {
+                                float* dz1, double* eval_acc, int* ticket, int B, int F1, int ncls, int ld_h1,
+                                int ld_dlogits, b200dp_stream_t s) {
     B200DP_REQUIRE(ncls >= 1 && ncls <= HT_MAXC, "ncls <= 16");
     B200DP_REQUIRE(F1 >= 1 && F1 <= 32 * HT_MAXK, "F1 <= 384");
     B200DP_REQUIRE(probs != nullptr || eval_acc == nullptr, "eval metrics need the probs buffer");
     B200DP_REQUIRE(loss_rows && loss_out && ticket, "loss_rows, loss_out and ticket are required");
-    HeadTailArgs a{h1, w, b, target, probs, loss_rows, loss_out, dlogits, dz1, eval_acc, ticket, B, F1, ncls, loss_mode};
+    HeadTailArgs a{h1, w, b, target, probs, loss_rows, loss_out, dlogits, dz1, eval_acc, ticket, B, F1, ncls, loss_mode,
+                   ld_h1 > 0 ? ld_h1 : F1, ld_dlogits > 0 ? ld_dlogits : ncls};
     const int grid = (B + HT_ROWS - 1) / HT_ROWS;
     const size_t smem = (size_t)(ncls * F1 + ncls) * sizeof(float);
     head_tail_kernel<<<grid, HT_ROWS * 32, smem, (cudaStream_t)s>>>(a);

@@ -128,15 +128,28 @@ __global__ void __launch_bounds__(RU_NT) reduce_update_kernel(RUArgs a) {
         const int parity = gen & 1u;
         const long sidx = (long)parity * a.comm.arena_len + idx;
         if (active) {
-            *reinterpret_cast<float4*>(a.comm.stage[a.comm.rank] + sidx) = g;
+            float* my_stage = nullptr;
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+                if (r == a.comm.rank) my_stage = a.comm.stage[r];
+            *reinterpret_cast<float4*>(my_stage + sidx) = g;
             __threadfence_system();
         }
         __syncthreads();
         const int slot = (a.start + off) / RU_FLAG_GRAIN;
         if (tid < world && tid != a.comm.rank) {
-            // publish to peer `tid`, then wait for peer `tid`'s publication of the same slice
-            st_release_sys(a.comm.flags[tid] + (long)a.comm.rank * a.comm.max_slices + slot, gen);
-            const uint32_t* mine = a.comm.flags[a.comm.rank] + (long)tid * a.comm.max_slices + slot;
+            // publish to peer `tid`, then wait for peer `tid`'s publication of the same slice.
+            // (pointer tables are read with compile-time indices: run-time indexing of kernel
+            // parameters compiles to slow indexed constant loads)
+            uint32_t* peer_flags = nullptr;
+            uint32_t* my_flags = nullptr;
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                if (r == tid) peer_flags = a.comm.flags[r];
+                if (r == a.comm.rank) my_flags = a.comm.flags[r];
+            }
+            st_release_sys(peer_flags + (long)a.comm.rank * a.comm.max_slices + slot, gen);
+            const uint32_t* mine = my_flags + (long)tid * a.comm.max_slices + slot;
             unsigned spins = 0;
             while ((int)(ld_acquire_sys(mine) - gen) < 0) {
                 if (++spins > RU_SPIN_LIMIT) { sTimeout = 1; break; }   // dead peer: error, not a hang
@@ -150,9 +163,16 @@ __global__ void __launch_bounds__(RU_NT) reduce_update_kernel(RUArgs a) {
         }
         if (active) {
             float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int r = 0; r < world; ++r) {            // rank order, identical on every rank
-                const float4 v = (r == a.comm.rank) ? g : ld_volatile_f4(a.comm.stage[r] + sidx);
-                sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
+            float4 v[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r)                  // all peer loads in flight together
+                if (r < world && r != a.comm.rank) v[r] = ld_volatile_f4(a.comm.stage[r] + sidx);
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {                // rank order, identical on every rank
+                if (r < world) {
+                    const float4 t = (r == a.comm.rank) ? g : v[r];
+                    sum.x += t.x; sum.y += t.y; sum.z += t.z; sum.w += t.w;
+                }
             }
             const float inv = 1.f / (float)world;
             g = make_float4(sum.x * inv, sum.y * inv, sum.z * inv, sum.w * inv);

@@ -47,7 +47,9 @@ struct TcProblem {
 struct TcGroup {
     TcProblem p[TC_MAX_PROBLEMS];
     int count;
+    long long* dbg;   // optional: CTA 0 writes clock64() stamps of its pipeline phases (profiling aid)
 };
+#define TC_STAMP(i) do { if (g.dbg && blockIdx.x == 0) g.dbg[i] = clock64(); } while (0)
 
 // ---- PTX wrappers -------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -117,6 +119,30 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, int mn_major) {
     return (uint64_t)((saddr & 0x3FFFF) >> 4) | (lbo << 16) | (sbo << 32) | (1ull << 46) | (layout << 61);
 }
 
+// Per-problem scalars pulled into registers once.  Indexing the kernel parameter with a run-time
+// problem index makes every later field access an indexed constant load (LDC c[0][R+off], ~100
+// cycles each, re-issued inside the loops); a switch over compile-time indices uses immediate
+// constant addresses and keeps the values in registers.
+struct TcScalars {
+    const CUtensorMap* tmA; const CUtensorMap* tmB;
+    const float* bias; const float* mask; float* out; float* colext;
+    int ld_mask, ld_out, M, N, K, a_mn, b_mn, act, tiles_n, tile_start;
+};
+__device__ __forceinline__ TcScalars tc_load_scalars(const TcGroup& g, int pi) {
+    TcScalars r;
+#define TC_COPY(i)                                                                                          \
+    case i: r.tmA = &g.p[i].tmA; r.tmB = &g.p[i].tmB; r.bias = g.p[i].bias; r.mask = g.p[i].mask;          \
+            r.out = g.p[i].out; r.colext = g.p[i].colext; r.ld_mask = g.p[i].ld_mask; r.ld_out = g.p[i].ld_out; \
+            r.M = g.p[i].M; r.N = g.p[i].N; r.K = g.p[i].K; r.a_mn = g.p[i].a_mn; r.b_mn = g.p[i].b_mn;      \
+            r.act = g.p[i].act; r.tiles_n = g.p[i].tiles_n; r.tile_start = g.p[i].tile_start; break;
+    switch (pi) {
+        TC_COPY(1) TC_COPY(2) TC_COPY(3)
+        default: TC_COPY(0)
+    }
+#undef TC_COPY
+    return r;
+}
+
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_constant__ TcGroup g) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;          // SWIZZLE_128B needs 1024 B alignment
@@ -128,11 +154,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) TC_STAMP(0);
     int pi = 0;
-#pragma unroll
-    for (int i = 1; i < TC_MAX_PROBLEMS; ++i)
-        if (i < g.count && (int)blockIdx.x >= g.p[i].tile_start) pi = i;
-    const TcProblem& P = g.p[pi];
+    if (g.count > 1 && (int)blockIdx.x >= g.p[1].tile_start) pi = 1;
+    if (g.count > 2 && (int)blockIdx.x >= g.p[2].tile_start) pi = 2;
+    if (g.count > 3 && (int)blockIdx.x >= g.p[3].tile_start) pi = 3;
+    const TcScalars P = tc_load_scalars(g, pi);
     const int tile = blockIdx.x - P.tile_start;
     const int tm = tile / P.tiles_n, tn = tile - tm * P.tiles_n;
     const int m0 = tm * TC_BM, n0 = tn * TC_BN;
@@ -148,6 +175,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
+    if (threadIdx.x == 0) TC_STAMP(1);
 
     if (warp == 0) {
         // ================= TMA producer =================
@@ -160,16 +188,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
                 const int k0 = s * TC_BK;
                 if (P.a_mn) {
 #pragma unroll
-                    for (int i = 0; i < TC_BM / 32; ++i) tma_load_2d(sa + i * (TC_BK * 128), &P.tmA, full_bar(st), m0 + 32 * i, k0);
+                    for (int i = 0; i < TC_BM / 32; ++i) tma_load_2d(sa + i * (TC_BK * 128), P.tmA, full_bar(st), m0 + 32 * i, k0);
                 } else {
-                    tma_load_2d(sa, &P.tmA, full_bar(st), k0, m0);
+                    tma_load_2d(sa, P.tmA, full_bar(st), k0, m0);
                 }
                 if (P.b_mn) {
 #pragma unroll
-                    for (int i = 0; i < TC_BN / 32; ++i) tma_load_2d(sb + i * (TC_BK * 128), &P.tmB, full_bar(st), n0 + 32 * i, k0);
+                    for (int i = 0; i < TC_BN / 32; ++i) tma_load_2d(sb + i * (TC_BK * 128), P.tmB, full_bar(st), n0 + 32 * i, k0);
                 } else {
-                    tma_load_2d(sb, &P.tmB, full_bar(st), k0, n0);
+                    tma_load_2d(sb, P.tmB, full_bar(st), k0, n0);
                 }
+                if (s < 8) TC_STAMP(8 + s);        // producer issued slab s
             }
         }
     } else if (warp == 1) {
@@ -183,6 +212,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
             const int st = s % TC_STAGES;
             mbar_wait(full_bar(st), (s / TC_STAGES) & 1);
             tc_fence_after();
+            if (lane == 0 && s < 8) TC_STAMP(16 + s);   // slab s landed
             if (lane == 0) {
                 const uint32_t sa = base + st * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
 #pragma unroll
@@ -199,39 +229,58 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         // ================= epilogue (warps 2..5) =================
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
+        if (threadIdx.x == 64) TC_STAMP(2);          // accumulator complete
         const int q = warp & 3;                           // TMEM lane quarter this warp may touch
-        const int m = m0 + q * 32 + lane;
         const int n_out = P.colext ? P.N - 1 : P.N;
+        // Stage the warp's 32x128 fp32 sub-tile through shared memory (the operand ring is idle now)
+        // so that global stores are row-contiguous: lane = column.  Row pitch 129 floats: both the
+        // row-wise writes (lane = row) and the column-wise reads (lane = column) are conflict-free.
+        constexpr int TP = TC_BN + 1;
+        float* sT = reinterpret_cast<float*>(smem_raw + (base - smem_u32(smem_raw))) + q * 32 * TP;
+        const int ncols = min(TC_BN, P.N - n0);           // warp-uniform
 #pragma unroll 1
-        for (int c = 0; c < TC_BN / 16; ++c) {
-            if (n0 + c * 16 >= P.N) break;                // warp-uniform
+        for (int c = 0; c * 16 < ncols; ++c) {
             uint32_t r[16];
             tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 16), r);
-            if (m < P.M) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const int n = n0 + c * 16 + j;
-                    if (n < P.N) {
-                        float v = __uint_as_float(r[j]);
-                        if (n < n_out) {
-                            if (P.bias) v += P.bias[n];
-                            if (P.act == 1) v = leaky(v);
-                            if (P.mask) v *= leaky_grad_from_act(P.mask[(long)m * P.ld_mask + n]);
-                            P.out[(long)m * P.ld_out + n] = v;
-                        } else {
-                            P.colext[m] = v;
-                        }
+            for (int j = 0; j < 16; ++j) sT[lane * TP + c * 16 + j] = __uint_as_float(r[j]);
+        }
+        __syncwarp();
+        float bias_r[TC_BN / 32];
+#pragma unroll
+        for (int cc = 0; cc < TC_BN / 32; ++cc) {
+            const int n = n0 + cc * 32 + lane;
+            bias_r[cc] = (P.bias && n < n_out) ? P.bias[n] : 0.f;
+        }
+        const int rows = min(32, P.M - (m0 + q * 32));    // warp-uniform, may be <= 0
+#pragma unroll 1
+        for (int rr = 0; rr < rows; ++rr) {
+            const int m = m0 + q * 32 + rr;
+#pragma unroll
+            for (int cc = 0; cc < TC_BN / 32; ++cc) {
+                const int n = n0 + cc * 32 + lane;
+                if (cc * 32 < ncols && n < P.N) {
+                    float v = sT[rr * TP + cc * 32 + lane];
+                    if (n < n_out) {
+                        v += bias_r[cc];
+                        if (P.act == 1) v = leaky(v);
+                        if (P.mask) v *= leaky_grad_from_act(P.mask[(long)m * P.ld_mask + n]);
+                        P.out[(long)m * P.ld_out + n] = v;
+                    } else {
+                        P.colext[m] = v;
                     }
                 }
             }
         }
     }
+    if (threadIdx.x == 64) TC_STAMP(3);              // epilogue of warp 2 done
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, TC_TMEM_COLS);
     }
+    if (threadIdx.x == 0) TC_STAMP(4);
 }
 
 // ---- host side ------------------------------------------------------------------------------------
@@ -275,11 +324,24 @@ static int encode_map(CUtensorMap* tm, const float* ptr, int rows, int cols, int
 
 using namespace b200dp;
 
+static int tc_launch(const b200dp_tc_problem* probs, int count, long long* dbg, b200dp_stream_t s);
+
 extern "C" int b200dp_tc_gemm_group(const b200dp_tc_problem* probs, int count, b200dp_stream_t s) {
+    return tc_launch(probs, count, nullptr, s);
+}
+// Profiling aid: same launch, CTA 0 writes clock64() stamps into dbg[0..32) (device memory):
+// [0] start, [1] setup done, [2] accumulator complete, [3] epilogue done, [4] end,
+// [8+s] producer issued slab s, [16+s] slab s landed (s < 8).
+extern "C" int b200dp_tc_gemm_group_timed(const b200dp_tc_problem* probs, int count, long long* dbg, b200dp_stream_t s) {
+    return tc_launch(probs, count, dbg, s);
+}
+
+static int tc_launch(const b200dp_tc_problem* probs, int count, long long* dbg, b200dp_stream_t s) {
     B200DP_REQUIRE(count >= 1 && count <= TC_MAX_PROBLEMS, "1..4 problems per launch");
     TcGroup g;
     memset(&g, 0, sizeof(g));
     g.count = count;
+    g.dbg = dbg;
     int total = 0;
     for (int i = 0; i < count; ++i) {
         const b200dp_tc_problem& q = probs[i];

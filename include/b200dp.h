@@ -32,6 +32,7 @@ typedef struct {
     int in_ch;
     int in_hw;   /* 28 (bilinear-upsampled to 32 on the fly) or 32 */
     int c1, c2, c3, f1, ncls;
+    int ld_p2;   /* row pitch (floats) of the pooled conv2 output p2 [B][ld_p2]; 0 = dense c2*25 */
 } b200dp_dims;
 
 int b200dp_version(void);
@@ -62,10 +63,12 @@ int b200dp_linear_fwd(const float* x, const float* w, const float* b, float* y, 
  * loss_out[0] = batch mean loss (deterministic fixed-order sum).
  * eval_acc (nullable): [0] += sum-reduced loss, [1] += #correct (double[2]) —
  * the eval loop of train.py:60-72 without per-batch host syncs.
- * dlogits/dz1 may be null in eval mode.  ticket: int[1] zero-initialised scratch. */
+ * dlogits/dz1 may be null in eval mode.  ticket: int[1] zero-initialised scratch.
+ * ld_h1 / ld_dlogits: row pitches of h1 and dlogits in floats (0 = dense F1 / ncls). */
 int b200dp_head_tail(const float* h1, const float* w, const float* b, const int64_t* target, int loss_mode,
                      float* probs, float* loss_rows, float* loss_out, float* dlogits, float* dz1,
-                     double* eval_acc, int* ticket, int B, int F1, int ncls, b200dp_stream_t s);
+                     double* eval_acc, int* ticket, int B, int F1, int ncls, int ld_h1, int ld_dlogits,
+                     b200dp_stream_t s);
 
 /* ---- backward ------------------------------------------------------------
  * Up to four independent GEMM-shaped backward problems in ONE launch.
@@ -101,6 +104,8 @@ typedef struct {
     float* colext;
 } b200dp_tc_problem;
 int b200dp_tc_gemm_group(const b200dp_tc_problem* probs, int count, b200dp_stream_t s);
+/* Profiling aid: same launch; CTA 0 records clock64() stamps of its pipeline phases in dbg[0..32). */
+int b200dp_tc_gemm_group_timed(const b200dp_tc_problem* probs, int count, long long* dbg, b200dp_stream_t s);
 
 /* Fused convolution backward for one step: pool2-bwd + leaky-bwd + conv2 dgrad
  * + conv2 wgrad/bgrad + pool1-bwd + leaky-bwd + conv1 wgrad/bgrad (no conv1

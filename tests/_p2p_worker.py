@@ -15,7 +15,7 @@ def train_native(ctx, cfg):
     torch.manual_seed(cfg["seed"])
     b = cfg["per_rank_batch"]
     st = NativeStepper(ctx, MNIST_LENET, OptHyper(cfg["opt"], lr=cfg["lr"]), batch=b, loss_mode="xent",
-                       graph=cfg["graph"], overlap=cfg["overlap"])
+                       graph=cfg["graph"], overlap=cfg["overlap"], dtype=cfg.get("dtype", "fp32"))
     g = torch.Generator().manual_seed(77)
     n_batches = cfg["n_batches"]
     gx = torch.randint(0, 256, (n_batches, ctx.world_size * b, 1, 28, 28), dtype=torch.uint8, generator=g)

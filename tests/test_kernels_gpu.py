@@ -172,16 +172,17 @@ def _eager_grads(model, x_f32, y, mode):
     return loss.detach(), {n: p.grad.detach().clone() for n, p in model.named_parameters()}
 
 
+@pytest.mark.parametrize("tc", [False, True])
 @pytest.mark.parametrize("mode", ["ref", "xent"])
 @pytest.mark.parametrize("b,u8", [(256, True), (37, False), (1, True)])
-def test_forward_backward_matches_autograd(mode, b, u8):
+def test_forward_backward_matches_autograd(mode, b, u8, tc):
     """All ten gradients of one fwd+bwd through the native kernels vs torch autograd."""
     from b200dp.data.synthetic import MNIST_SPEC
     from b200dp.models.fused import NativeLeNet
     torch.manual_seed(5)
     dev = torch.device("cuda")
     ref = LeNet().to(dev).double()
-    net = NativeLeNet(MNIST_LENET, 256, dev, loss_mode=mode)
+    net = NativeLeNet(MNIST_LENET, 256, dev, loss_mode=mode, tc=tc)
     with torch.no_grad():
         for (n, p), (_, q) in zip(net.module.named_parameters(), ref.named_parameters()):
             q.copy_(p.double())
@@ -196,7 +197,7 @@ def test_forward_backward_matches_autograd(mode, b, u8):
     net.forward(x, y, train=True)
     net.backward(x)
     torch.cuda.synchronize()
-    assert abs(float(net.loss) - float(loss_ref)) < 1e-5
+    assert abs(float(net.loss) - float(loss_ref)) < (2e-3 if tc else 1e-5)
     got = {n: net.g[n].clone() for n in net.g}
     conv = net.partials[: net.cur_partials].double().sum(0)
     for name, off in zip(("ConvNet.1.weight", "ConvNet.1.bias", "ConvNet.4.weight", "ConvNet.4.bias"), net.conv_offsets):
@@ -204,7 +205,7 @@ def test_forward_backward_matches_autograd(mode, b, u8):
     for n, gr in g_ref.items():
         scale = gr.abs().max().clamp_min(1e-12)
         err = (got[n].double() - gr).abs().max() / scale
-        assert err < 2e-4, (n, float(err))
+        assert err < (8e-2 if tc else 2e-4), (n, float(err))      # tf32 tensor-core GEMMs vs exact fp32
 
 
 @pytest.mark.parametrize("kind", ["adadelta", "sgd", "adam"])
@@ -257,9 +258,10 @@ def test_reduce_update_partials_deterministic():
     assert torch.allclose(outs[0][0], -outs[0][1])
 
 
+@pytest.mark.parametrize("dtype", ["fp32", "tf32"])
 @pytest.mark.parametrize("opt", ["adadelta", "sgd", "adam"])
 @pytest.mark.parametrize("graph", [False, True])
-def test_train_steps_match_eager(opt, graph):
+def test_train_steps_match_eager(opt, graph, dtype):
     """N full steps (fwd, bwd, fused update; optionally CUDA-graph replay) vs the eager stepper."""
     from b200dp.engine import EagerStepper
     from b200dp.models.fused import NativeStepper
@@ -270,20 +272,23 @@ def test_train_steps_match_eager(opt, graph):
     ctx = RankContext(0, 1, 0, dev, "nccl")
     lr = {"adadelta": 0.1, "sgd": 0.05, "adam": 1e-3}[opt]
     eager = EagerStepper(ctx, MNIST_LENET, OptHyper(opt, lr=lr), loss_mode="xent")
-    native_s = NativeStepper(ctx, MNIST_LENET, OptHyper(opt, lr=lr), batch=64, loss_mode="xent", graph=graph)
+    native_s = NativeStepper(ctx, MNIST_LENET, OptHyper(opt, lr=lr), batch=64, loss_mode="xent", graph=graph,
+                             dtype=dtype)
     native_s.model.load_state_dict(eager.model.state_dict())
+    loose = 10.0 if dtype == "tf32" else 1.0
     xs = [torch.randint(0, 256, (64, 1, 28, 28), dtype=torch.uint8, device=dev) for _ in range(3)]
     ys = [torch.randint(0, 10, (64,), device=dev) for _ in range(3)]
     for i in range(9):
         le = float(eager.train_step(xs[i % 3], ys[i % 3]))
         ln = float(native_s.train_step(xs[i % 3], ys[i % 3]))
-        assert abs(le - ln) < 5e-4 * max(1.0, abs(le)), (i, le, ln)
-    for (n, a), (_, b) in zip(eager.model.state_dict().items(), native_s.model.state_dict().items()):
-        assert torch.allclose(a, b, atol=5e-4, rtol=5e-3), (n, (a - b).abs().max())
+        assert abs(le - ln) < 5e-4 * loose * max(1.0, abs(le)), (i, le, ln)
+    if dtype == "fp32" or opt == "sgd":   # adaptive optimizers amplify tf32 round-off in tiny gradients
+        for (n, a), (_, b) in zip(eager.model.state_dict().items(), native_s.model.state_dict().items()):
+            assert torch.allclose(a, b, atol=5e-4 * loose, rtol=5e-3 * loose), (n, (a - b).abs().max())
     # eval path
     eager.eval_batch(xs[0], ys[0]); native_s.eval_batch(xs[0], ys[0])
     (l0, c0), (l1, c1) = eager.eval_result(), native_s.eval_result()
-    assert abs(l0 - l1) < 1e-2 and abs(c0 - c1) <= 1
+    assert abs(l0 - l1) < 2e-4 * loose * max(1.0, abs(l0)) and abs(c0 - c1) <= 1
 
 
 def test_ragged_batch_after_full_batch():
@@ -296,7 +301,8 @@ def test_ragged_batch_after_full_batch():
     dev = torch.device("cuda", 0)
     ctx = RankContext(0, 1, 0, dev, "nccl")
     eager = EagerStepper(ctx, MNIST_LENET, OptHyper("sgd", lr=0.05), loss_mode="xent")
-    nat = NativeStepper(ctx, MNIST_LENET, OptHyper("sgd", lr=0.05), batch=64, loss_mode="xent", graph=True)
+    nat = NativeStepper(ctx, MNIST_LENET, OptHyper("sgd", lr=0.05), batch=64, loss_mode="xent", graph=True,
+                        dtype="fp32")
     nat.model.load_state_dict(eager.model.state_dict())
     for b in (64, 64, 64, 64, 23, 64, 5):
         x = torch.randint(0, 256, (b, 1, 28, 28), dtype=torch.uint8, device=dev)

@@ -62,7 +62,7 @@ def test_p2p_deterministic_under_skew(tmp_path, world):
     _need(world)
     from b200dp.parallel import launch
     base = {"seed": 5, "per_rank_batch": 32, "n_batches": 4, "steps": 150, "opt": "adadelta", "lr": 0.1,
-            "out": str(tmp_path)}
+            "out": str(tmp_path), "dtype": "tf32"}
     runs = {"plain": dict(graph=True, overlap=True, jitter=False), "skew": dict(graph=True, overlap=True, jitter=True),
             "nograph": dict(graph=False, overlap=False, jitter=True)}
     outs = {}
