@@ -38,9 +38,10 @@ def build_parser() -> argparse.ArgumentParser:
                    help="gradient path: b200 = fused P2P kernels (default on GPU), nccl/gloo = torch.distributed")
     p.add_argument("--world-size", type=int, default=0, help="ranks to spawn (0 = one per visible GPU)")
     p.add_argument("--cpu", action="store_true", help="run on CPU with gloo instead of exiting when no GPU")
-    p.add_argument("--dtype", choices=["fp32", "tf32", "bf16"], default="tf32",
+    p.add_argument("--dtype", choices=["auto", "fp32", "tf32", "bf16"], default="auto",
                    help="fp32 = exact CUDA-core kernels; tf32 = tcgen05 tensor-core GEMMs (fp32 storage and "
-                        "accumulation; bf16 is accepted as an alias); master weights are always fp32")
+                        "accumulation; bf16 is accepted as an alias); auto = whichever is faster for the model "
+                        "size; master weights are always fp32")
     p.add_argument("--optimizer", choices=["adadelta", "sgd", "adam"], default="adadelta")
     p.add_argument("--momentum", type=float, default=0.9)
     p.add_argument("--weight-decay", type=float, default=0.0)

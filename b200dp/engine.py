@@ -135,7 +135,7 @@ def build_stepper(ctx: RankContext, args, cfg: LeNetConfig, hyper: OptHyper, spe
                              algo=getattr(args, "allreduce_algo", "auto"),
                              graph=not getattr(args, "no_graph", False),
                              overlap=not getattr(args, "no_overlap", False),
-                             dtype=getattr(args, "dtype", "tf32"))
+                             dtype=getattr(args, "dtype", "auto"))
     return EagerStepper(ctx, cfg, hyper, loss_mode=args.loss, spec=spec,
                         bucket_bytes=getattr(args, "bucket_bytes", -1),
                         overlap=not getattr(args, "no_overlap", False))

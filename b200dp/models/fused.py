@@ -190,11 +190,15 @@ class NativeStepper:
 
     def __init__(self, ctx, cfg: LeNetConfig, hyper: OptHyper, *, batch: int, loss_mode: str = "ref",
                  spec: ImageSpec = MNIST_SPEC, algo: str = "auto", graph: bool = True, overlap: bool = True,
-                 dtype: str = "tf32", module: Optional[LeNet] = None):
+                 dtype: str = "auto", module: Optional[LeNet] = None):
         self.ctx, self.cfg = ctx, cfg
         self.device = ctx.device
-        if dtype not in ("fp32", "tf32", "bf16"):
+        if dtype not in ("auto", "fp32", "tf32", "bf16"):
             raise ValueError(f"unknown dtype {dtype!r}")
+        if dtype == "auto":
+            # measured on B200 (profiles/): at the reference model's size (GEMMs of <= 25 MFLOP) the CUDA-core
+            # kernels finish sooner than one tcgen05 pipeline fill; the tensor-core path wins for the wide model
+            dtype = "tf32" if cfg.width_mult > 1 else "fp32"
         self.dtype = "fp32" if dtype == "fp32" else "tf32"      # "bf16" is accepted as a request for the tensor-core path
         self.net = NativeLeNet(cfg, batch, self.device, loss_mode=loss_mode, spec=spec, module=module,
                                tc=self.dtype != "fp32")

@@ -52,7 +52,7 @@ def _parse():
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--no-overlap", action="store_true")
     p.add_argument("--input", choices=["u8", "f32"], default="u8", help="host->device input format (e2e)")
-    p.add_argument("--dtype", choices=["fp32", "tf32"], default="tf32",
+    p.add_argument("--dtype", choices=["auto", "fp32", "tf32"], default="auto",
                    help="tf32 = tcgen05 tensor-core GEMMs on fp32 tensors; fp32 = exact CUDA-core kernels")
     return p.parse_args()
 
@@ -185,7 +185,7 @@ def run_own(args):
             "ms_per_step": ms / K, "higher_is_better": True,
             "scaling": "strong" if args.config == "strong4096" else "weak",
             "vs_baseline": None,
-            "dtype": "tf32 tensor-core GEMMs (fp32 storage/accumulate), fp32 convs" if args.dtype == "tf32" else "fp32",
+            "dtype": "tf32 tensor-core GEMMs (fp32 storage/accumulate), fp32 convs" if stepper.dtype == "tf32" else "fp32",
             "data": "synthetic", "impl": "b200dp",
             "config": {"model": "cnn.py LeNet" if args.config != "wide_cifar" else "cnn.py LeNet 4x wide, CIFAR-shaped",
                        "global_batch": batch * world, "per_gpu_batch": batch, "seq_len": None,

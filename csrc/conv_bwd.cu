@@ -15,7 +15,7 @@
 namespace b200dp {
 
 constexpr int CB_NT = 256;
-constexpr int CB_MAX_PARTIALS = 128;
+constexpr int CB_MAX_PARTIALS = 256;
 constexpr int ZP = 18;  // 10x10 conv2-output map zero-padded by 4 on each side
 
 struct ConvBwdArgs {
@@ -44,11 +44,11 @@ struct ConvBwdCfg {
                          F_W2F = C2 * 25 * C1P, F_PART = OG * C1 * 196, F_G1 = C1 * 196, F_G2 = C2 * 25,
                          I_POS2 = C2 * 25;
     static constexpr size_t SMEM = (size_t)(F_X0 + F_RAW + F_P1 + F_DZ2 + F_W2F + F_PART + F_G1 + F_G2 + I_POS2) * 4
-                                   + (size_t)(C1 * 196 + 15) / 16 * 16;
+                                   + (size_t)(C1 * 196 * 2 + 15) / 16 * 16;
 };
 
 template <int C0, int C1, int C2>
-__global__ void __launch_bounds__(CB_NT) conv_bwd_kernel(ConvBwdArgs a) {
+__global__ void __launch_bounds__(CB_NT, 2) conv_bwd_kernel(ConvBwdArgs a) {
     using C = ConvBwdCfg<C0, C1, C2>;
     extern __shared__ __align__(16) float smem[];
     float* sX0 = smem;
@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(CB_NT) conv_bwd_kernel(ConvBwdArgs a) {
     float* sG1 = sPart + C::F_PART;    // dL/d(conv1 pre-activation) at the pooled argmax, [C1][196]
     float* sG2 = sG1 + C::F_G1;        // dL/d(conv2 pre-activation) at the pooled argmax, [C2][25]
     int* sPos2 = reinterpret_cast<int*>(sG2 + C::F_G2);            // y*,x* packed: y*<<8 | x*
-    uint8_t* sIdx1 = reinterpret_cast<uint8_t*>(sPos2 + C::I_POS2);
+    uint16_t* sOff1 = reinterpret_cast<uint16_t*>(sPos2 + C::I_POS2);   // argmax position in the 32x32 input, per (c, cell)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int hw = a.in_hw, n_in = hw * hw;
@@ -88,13 +88,14 @@ __global__ void __launch_bounds__(CB_NT) conv_bwd_kernel(ConvBwdArgs a) {
             sRaw[i] = load_pixel(a.x, a.in_is_u8, (long)img * C0 * n_in + i, a.mean, a.std);
         for (int i = tid; i < C1 * 196; i += CB_NT) {
             sP1[i] = a.p1[(long)img * C1 * 196 + i];
-            sIdx1[i] = a.idx1[(long)img * C1 * 196 + i];
+            const int pp = i % 196, py = pp / 14, px = pp - py * 14, k = a.idx1[(long)img * C1 * 196 + i];
+            sOff1[i] = (uint16_t)((2 * py + (k >> 1)) * 32 + 2 * px + (k & 1));
         }
         for (int i = tid; i < C2 * 25; i += CB_NT) {
             const long o = (long)img * C2 * 25 + i;
             const int pp = i % 25, py = pp / 5, px = pp - py * 5, k = a.idx2[o];
             sG2[i] = a.dp2[o] * leaky_grad_from_act(a.p2[(long)img * a.ld_p2 + i]);
-            sPos2[i] = ((2 * py + (k >> 1)) << 8) | (2 * px + (k & 1));
+            sPos2[i] = ((2 * py + (k >> 1)) << 8) | (2 * px + (k & 1));   // (y*, x*) of the conv2 output
         }
         for (int i = tid; i < C::F_DZ2; i += CB_NT) sdZ2[i] = 0.f;
         __syncthreads();
@@ -190,11 +191,8 @@ __global__ void __launch_bounds__(CB_NT) conv_bwd_kernel(ConvBwdArgs a) {
                 const int ky = t / 5, kx = t - ky * 5;
                 const float* xin = sX0 + i0 * 1024 + ky * 32 + kx;
                 float s = 0.f;
-#pragma unroll 4
-                for (int pp = 0; pp < 196; ++pp) {
-                    const int py = pp / 14, px = pp - py * 14, k = sIdx1[c * 196 + pp];
-                    s = fmaf(sG1[c * 196 + pp], xin[(2 * py + (k >> 1)) * 32 + 2 * px + (k & 1)], s);
-                }
+#pragma unroll 7
+                for (int pp = 0; pp < 196; ++pp) s = fmaf(sG1[c * 196 + pp], xin[sOff1[c * 196 + pp]], s);
                 acc_w1[j] += s;
             }
         }
@@ -223,7 +221,7 @@ __global__ void __launch_bounds__(CB_NT) conv_bwd_kernel(ConvBwdArgs a) {
 }
 
 static int num_partials_for(int B) {
-    int n = (B + 1) / 2;
+    int n = B;     // one image per CTA while rows last: two or three CTAs share an SM and overlap their phases
     if (n > CB_MAX_PARTIALS) n = CB_MAX_PARTIALS;
     return n < 1 ? 1 : n;
 }
@@ -269,11 +267,11 @@ extern "C" int b200dp_conv_bwd(const void* x, int in_is_u8, float mean, float st
 // this entry point keeps those rows in a fixed array that is part of the library image instead,
 // sums them, and hands back only the four finished gradients.
 //
-// The array is B200DP_NOALLOC_MAX_ROWS x B200DP_NOALLOC_MAX_STRIDE floats (1,376,256 bytes).  Every
+// The array is B200DP_NOALLOC_MAX_ROWS x B200DP_NOALLOC_MAX_STRIDE floats (2,752,512 bytes).  Every
 // GPU that loads this library carries it from load until the process exits, used or not.
 namespace b200dp {
 
-constexpr int NA_MAX_ROWS = CB_MAX_PARTIALS;   // 128 == B200DP_NOALLOC_MAX_ROWS
+constexpr int NA_MAX_ROWS = CB_MAX_PARTIALS;   // 256 == B200DP_NOALLOC_MAX_ROWS
 constexpr int NA_MAX_STRIDE = 2688;            //        B200DP_NOALLOC_MAX_STRIDE
 constexpr int NA_MAX_DEVICES = 64;
 

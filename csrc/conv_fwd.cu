@@ -167,7 +167,7 @@ extern "C" int b200dp_conv2_fwd(const float* p1, const float* w, const float* b,
                                 b200dp_dims d, b200dp_stream_t s) {
     ConvFwdArgs a{p1, w, b, p2, idx2, d.batch, 0, 14, 0.f, 1.f, d.ld_p2 > 0 ? d.ld_p2 : d.c2 * 25};
     B200DP_REQUIRE(a.out_img_stride >= d.c2 * 25, "ld_p2 smaller than c2*25");
-    if (d.c1 == 6 && d.c2 == 16) return launch_conv_fwd<6, 16, 14, 4, 4, 2, false>(a, (cudaStream_t)s);
+    if (d.c1 == 6 && d.c2 == 16) return launch_conv_fwd<6, 16, 14, 4, 4, 1, false>(a, (cudaStream_t)s);
     if (d.c1 == 24 && d.c2 == 64) return launch_conv_fwd<24, 64, 14, 4, 4, 2, false>(a, (cudaStream_t)s);
     B200DP_REQUIRE(false, "unsupported (c1, c2): expected (6,16) or (24,64)");
 }

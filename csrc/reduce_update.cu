@@ -107,8 +107,18 @@ __global__ void __launch_bounds__(RU_NT) reduce_update_kernel(RUArgs a) {
         // slice == RU_PSLICE: thread (o = tid%32, pg = tid/32) sums rows pg, pg+8, ... ; then 8 -> 1
         const int o = tid & 31, pg = tid >> 5;
         float s = 0.f;
-        if (o < n_here)
-            for (int r = pg; r < a.n_partials; r += 8) s += __ldcg(a.partials + (long)r * a.partial_stride + off + o);
+        if (o < n_here) {
+            const float* src = a.partials + off + o;
+            int r = pg;
+            for (; r + 56 < a.n_partials; r += 64) {          // 8 independent loads in flight, added in row order
+                float t[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) t[u] = __ldcg(src + (long)(r + 8 * u) * a.partial_stride);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) s += t[u];
+            }
+            for (; r < a.n_partials; r += 8) s += __ldcg(src + (long)r * a.partial_stride);
+        }
         sRed[pg][o] = s;
         __syncthreads();
         if (tid < RU_PSLICE) {

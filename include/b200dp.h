@@ -127,7 +127,7 @@ int b200dp_conv_bwd(const void* x, int in_is_u8, float mean, float std, const fl
  * library).  For hosts that cannot call cudaMalloc at the point where they call us — for example
  * because one pool allocator already owns all device memory, or because the call sits in a loop
  * whose latency budget has no room for an allocation.  The partial-gradient rows live in an array
- * built into the library (B200DP_NOALLOC_MAX_ROWS x B200DP_NOALLOC_MAX_STRIDE floats = 1,376,256
+ * built into the library (B200DP_NOALLOC_MAX_ROWS x B200DP_NOALLOC_MAX_STRIDE floats = 2,752,512
  * bytes, resident on every GPU that loads the library until the process exits); the call sums
  * them in fixed order and writes only the four finished gradients:
  *     grad_out[off_w1 .. +150)  dL/dW conv1      grad_out[off_b1 .. +6)   dL/db conv1
@@ -139,7 +139,7 @@ int b200dp_conv_bwd(const void* x, int in_is_u8, float mean, float std, const fl
  * attribute; make that first call before any stream capture begins.  All calls on a device share
  * the one array: two calls whose kernels can overlap on the GPU (different streams, no ordering
  * between them) race on it — order them.  Nothing has to be cleared between calls. */
-#define B200DP_NOALLOC_MAX_ROWS 128
+#define B200DP_NOALLOC_MAX_ROWS 256
 #define B200DP_NOALLOC_MAX_STRIDE 2688
 int b200dp_conv_bwd_noalloc(const void* x, int in_is_u8, float mean, float std, const float* p1,
                             const uint8_t* idx1, const float* p2, const uint8_t* idx2, const float* dp2,
