@@ -240,7 +240,8 @@ class NativeStepper:
         native.reduce_update(self.arena.param, self.arena.grad, opt.state0, opt.state1, None, b.start, b.numel,
                              net.partials if is_conv else None, net.cur_partials if is_conv else 0,
                              net.partial_stride if is_conv else 0, opt.hyper.code(), self.hyper_dev,
-                             self.step_counter, bucket_index == 2, self.comm.struct if self.comm else None)
+                             self.step_counter, bucket_index == 2,
+                             self.comm.struct_for(b.numel * 4) if self.comm else None)
 
     def _step_body(self, x: torch.Tensor, y: torch.Tensor) -> None:
         main = torch.cuda.current_stream(self.device)

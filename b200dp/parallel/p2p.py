@@ -2,17 +2,28 @@
 
 Replaces the NCCL communicator the reference obtains from
 ``dist.init_process_group('nccl')`` (train.py:26-31).  torch.distributed is the
-bootstrap channel only: each rank allocates one block (staging buffers for two
-step parities + flag slots), exports a 64-byte CUDA IPC handle, the handles are
-all-gathered once, every rank maps every peer's block.  From then on
-``csrc/reduce_update.cu`` reads and writes peer memory directly over NVLink.
+bootstrap channel only; after set-up ``csrc/reduce_update.cu`` reads and writes
+peer memory directly over NVLink.
 
-Block layout per rank (bytes):
-    [0, 2*arena_len*4)                      staging, parity 0 then parity 1 (fp32)
-    [flag_off, flag_off + 8*max_slices*4)   flags[src_rank][slice] (uint32 generation)
+Two transports provide the peer mappings:
+
+``ipc``   our own plumbing: ``cudaMalloc`` + CUDA IPC handles (64 opaque bytes
+          each, all-gathered once).  No multicast, so algorithms 0 (one-shot)
+          and 1 (two-shot).
+``symm``  ``torch.distributed._symmetric_memory`` (cuMem VMM + multicast
+          object): additionally yields the NVSwitch multicast alias needed by
+          algorithm 2 (NVLS ``multimem.ld_reduce`` / ``multimem.st``).
+
+Block layout per rank (floats / words), identical on every rank:
+    stage : [2 parities][arena_len] published slices, then [arena_len] landing
+            area for reduced slices (two-shot / NVLS)
+    flags : [8 source ranks][max_slices] "slice published", then [max_slices]
+            "reduced slice delivered"; generation numbers that only ever grow
 """
 from __future__ import annotations
 
+import copy
+import warnings
 from typing import List, Optional
 
 import torch
@@ -22,38 +33,100 @@ from ..ops import native
 
 FLAG_GRAIN = 32   # csrc/reduce_update.cu RU_FLAG_GRAIN
 MAX_WORLD = 8
+ALGO_CODES = {"oneshot": 0, "twoshot": 1, "nvls": 2}
+# measured cross-over on 8xB200 (profiles/allreduce_sweep.md): below this a single exchange wins
+ONESHOT_MAX_BYTES = 512 * 1024
 
 
 class P2PComm:
-    def __init__(self, arena_len: int, rank: int, world: int, algo: str = "auto"):
+    def __init__(self, arena_len: int, rank: int, world: int, algo: str = "auto", transport: str = "auto"):
         if world > MAX_WORLD:
             raise ValueError(f"world size {world} > {MAX_WORLD} (single NVSwitch node)")
-        self.rank, self.world, self.arena_len = rank, world, arena_len
+        if algo not in ("auto", "oneshot", "twoshot", "nvls"):
+            raise ValueError(f"unknown all-reduce algorithm {algo!r}")
+        self.rank, self.world, self.arena_len, self.algo = rank, world, arena_len, algo
         self.max_slices = (arena_len + FLAG_GRAIN - 1) // FLAG_GRAIN
-        self.stage_bytes = 2 * arena_len * 4
+        self.stage_bytes = 3 * arena_len * 4
         self.flag_off = (self.stage_bytes + 255) // 256 * 256
-        self.total_bytes = self.flag_off + MAX_WORLD * self.max_slices * 4
-        self.algo = {"auto": 0, "oneshot": 0, "twoshot": 1, "nvls": 2}[algo]
+        self.total_bytes = self.flag_off + (MAX_WORLD + 1) * self.max_slices * 4
         self.local_ptr: Optional[int] = None
         self.peer_ptrs: List[Optional[int]] = [None] * world
+        self.multicast_ptr = 0
+        self.transport = "none"
+        self._symm_tensor = None
+        self._symm_handle = None
         self.struct = native.Comm()
-        self.struct.world, self.struct.rank, self.struct.algo = world, rank, 0 if algo == "auto" else self.algo
+        self.struct.world, self.struct.rank, self.struct.algo = world, rank, 0
         self.struct.arena_len, self.struct.max_slices = arena_len, self.max_slices
         self.struct.mc_stage = None
+        self._by_algo = {}
         if world > 1:
-            self._setup()
+            # CUDA IPC is the default; torch symmetric memory is only needed (and only tried) for the
+            # multicast alias that NVLS requires
+            want_symm = transport == "symm" or (transport == "auto" and algo == "nvls")
+            if not (want_symm and self._setup_symm()):
+                self._setup_ipc()
+            for r in range(world):
+                self.struct.stage[r] = self.peer_ptrs[r]
+                self.struct.flags[r] = self.peer_ptrs[r] + self.flag_off
+            self.struct.mc_stage = self.multicast_ptr or None
+            if algo == "nvls" and not self.multicast_ptr:
+                warnings.warn("NVLS multicast is not available on this system; using the two-shot P2P algorithm")
+            dist.barrier()   # nobody launches before every mapping exists
 
-    def _setup(self) -> None:
+    # -- transports ---------------------------------------------------------------
+    def _setup_ipc(self) -> None:
         self.local_ptr = native.symm_alloc(self.total_bytes)
         handle = native.symm_export(self.local_ptr)
         handles: List[Optional[bytes]] = [None] * self.world
         dist.all_gather_object(handles, handle)
         for r in range(self.world):
             self.peer_ptrs[r] = self.local_ptr if r == self.rank else native.symm_import(handles[r])
-        for r in range(self.world):
-            self.struct.stage[r] = self.peer_ptrs[r]
-            self.struct.flags[r] = self.peer_ptrs[r] + self.flag_off
-        dist.barrier()   # nobody launches before every mapping exists
+        self.transport = "ipc"
+
+    def _setup_symm(self) -> bool:
+        ok = 1
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            t = symm_mem.empty(self.total_bytes, dtype=torch.uint8, device=torch.device("cuda", torch.cuda.current_device()))
+            t.zero_()
+            torch.cuda.synchronize()
+            hdl = symm_mem.rendezvous(t, dist.group.WORLD)
+            ptrs = [int(p) for p in hdl.buffer_ptrs]
+            mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        except Exception as e:  # no VMM / fabric support in this container: fall back to CUDA IPC
+            warnings.warn(f"torch symmetric memory unavailable ({type(e).__name__}: {e}); using CUDA IPC")
+            ok = 0
+        flag = torch.tensor([ok], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)      # all ranks must agree on the transport
+        if int(flag.item()) == 0:
+            return False
+        self._symm_tensor, self._symm_handle = t, hdl
+        self.peer_ptrs = ptrs
+        self.local_ptr = ptrs[self.rank]
+        self.multicast_ptr = mc
+        self.transport = "symm"
+        return True
+
+    # -- per-bucket algorithm choice ---------------------------------------------------
+    def struct_for(self, bucket_bytes: int) -> "native.Comm":
+        """The ``b200dp_comm`` to pass for a bucket of this size (algorithm chosen per bucket)."""
+        algo = self.algo
+        if algo == "auto":
+            algo = "oneshot" if bucket_bytes <= ONESHOT_MAX_BYTES else ("nvls" if self.multicast_ptr else "twoshot")
+        if algo == "nvls" and not self.multicast_ptr:
+            algo = "twoshot"
+        st = self._by_algo.get(algo)
+        if st is None:
+            st = native.Comm()
+            st.world, st.rank, st.algo = self.world, self.rank, ALGO_CODES[algo]
+            st.arena_len, st.max_slices = self.arena_len, self.max_slices
+            for r in range(self.world):
+                st.stage[r] = self.struct.stage[r]
+                st.flags[r] = self.struct.flags[r]
+            st.mc_stage = self.multicast_ptr or None
+            self._by_algo[algo] = st
+        return st
 
     def close(self) -> None:
         if self.local_ptr is None:
@@ -64,9 +137,11 @@ class P2PComm:
                 dist.barrier()   # peers must stop touching our block before it goes away
             except Exception:
                 pass
-        for r, p in enumerate(self.peer_ptrs):
-            if p is not None and r != self.rank:
-                native.symm_close(p)
-        native.symm_free(self.local_ptr)
+        if self.transport == "ipc":
+            for r, p in enumerate(self.peer_ptrs):
+                if p is not None and r != self.rank:
+                    native.symm_close(p)
+            native.symm_free(self.local_ptr)
+        self._symm_tensor = self._symm_handle = None
         self.local_ptr = None
         self.peer_ptrs = [None] * self.world

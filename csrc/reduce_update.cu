@@ -8,7 +8,7 @@
 // Decomposition: CTA j owns slice j of the bucket, end to end.  A slice never depends on another
 // slice, so no grid-wide synchronisation exists anywhere:
 //   A. (optional) sum the partial-gradient rows written by the conv backward (fixed order).
-//   B. world > 1, one-shot P2P: store the local slice into this rank's staging buffer
+//   B. world > 1 (one-shot shown; two-shot and NVLS below): store the local slice into this rank's staging buffer
 //      [parity][arena], __threadfence_system, then write the generation number into flag slot
 //      (my_rank, slice) of EVERY peer (st.release.sys over NVLink); spin (ld.acquire.sys, bounded)
 //      on the local flag slots (peer, slice); read the slice from every rank's staging buffer with
@@ -25,7 +25,8 @@
 namespace b200dp {
 
 constexpr int RU_NT = 256;
-constexpr int RU_SLICE = 1024;        // floats per CTA for plain buckets (float4 per thread)
+constexpr int RU_CHUNK = 1024;        // floats per CTA iteration (float4 per thread)
+constexpr int RU_MAX_CTAS = 148 * 8;  // large buckets: at most this many CTAs, each looping over chunks
 constexpr int RU_PSLICE = 32;         // floats per CTA when partial rows are pre-reduced
 constexpr int RU_FLAG_GRAIN = 32;     // one flag slot per 32 arena floats
 constexpr unsigned RU_SPIN_LIMIT = 1u << 28;
@@ -56,6 +57,18 @@ __device__ __forceinline__ float4 ld_volatile_f4(const float* p) {
                  : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
     return v;
 }
+// NVLS: a load from / store to the multicast alias of the staging buffers is executed by the
+// NVSwitch on every rank's copy (sm_90+; the alias comes from cuMulticast* / torch symmetric memory).
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float* mc, const float4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 __device__ __forceinline__ uint16_t f32_to_bf16_rn(float f) {
     uint32_t u = __float_as_uint(f);
     if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40u);
@@ -65,27 +78,76 @@ __device__ __forceinline__ uint16_t f32_to_bf16_rn(float f) {
 
 struct OptScalars { float lr, h0, h1, h2, wd, c0, c1; };
 
+// Every operation is an explicit round-to-nearest intrinsic: the compiler may not contract or
+// re-associate, so the two code paths of the two-shot algorithm (owner / non-owner) and every rank
+// produce bit-identical parameters from the same summed gradient.
 __device__ __forceinline__ void opt_apply(int kind, const OptScalars& h, float g, float& p, float& s0, float& s1) {
-    if (h.wd != 0.f) g = fmaf(h.wd, p, g);
+    if (h.wd != 0.f) g = __fmaf_rn(h.wd, p, g);
     if (kind == 0) {            // Adadelta: h0 = rho, h1 = eps
-        s0 = h.h0 * s0 + (1.f - h.h0) * g * g;
-        const float stdv = sqrtf(s0 + h.h1);
-        const float delta = sqrtf(s1 + h.h1) / stdv * g;
-        s1 = h.h0 * s1 + (1.f - h.h0) * delta * delta;
-        p -= h.lr * delta;
+        const float omr = __fsub_rn(1.f, h.h0);
+        s0 = __fmaf_rn(h.h0, s0, __fmul_rn(omr, __fmul_rn(g, g)));
+        const float stdv = __fsqrt_rn(__fadd_rn(s0, h.h1));
+        const float delta = __fmul_rn(__fdiv_rn(__fsqrt_rn(__fadd_rn(s1, h.h1)), stdv), g);
+        s1 = __fmaf_rn(h.h0, s1, __fmul_rn(omr, __fmul_rn(delta, delta)));
+        p = __fsub_rn(p, __fmul_rn(h.lr, delta));
     } else if (kind == 1) {     // SGD: h0 = momentum, h1 = nesterov flag
         float d = g;
         if (h.h0 != 0.f) {
-            s0 = h.h0 * s0 + g;
-            d = (h.h1 != 0.f) ? g + h.h0 * s0 : s0;
+            s0 = __fmaf_rn(h.h0, s0, g);
+            d = (h.h1 != 0.f) ? __fmaf_rn(h.h0, s0, g) : s0;
         }
-        p -= h.lr * d;
+        p = __fsub_rn(p, __fmul_rn(h.lr, d));
     } else {                    // Adam: h0 = beta1, h1 = beta2, h2 = eps; c0 = 1/bc1, c1 = 1/sqrt(bc2)
-        s0 = h.h0 * s0 + (1.f - h.h0) * g;
-        s1 = h.h1 * s1 + (1.f - h.h1) * g * g;
-        const float denom = sqrtf(s1) * h.c1 + h.h2;
-        p -= (h.lr * h.c0) * (s0 / denom);
+        s0 = __fmaf_rn(h.h0, s0, __fmul_rn(__fsub_rn(1.f, h.h0), g));
+        s1 = __fmaf_rn(h.h1, s1, __fmul_rn(__fsub_rn(1.f, h.h1), __fmul_rn(g, g)));
+        const float denom = __fmaf_rn(__fsqrt_rn(s1), h.c1, h.h2);
+        p = __fsub_rn(p, __fmul_rn(__fmul_rn(h.lr, h.c0), __fdiv_rn(s0, denom)));
     }
+}
+
+__device__ __forceinline__ float4 scale4(const float4& v, float k) {
+    return make_float4(__fmul_rn(v.x, k), __fmul_rn(v.y, k), __fmul_rn(v.z, k), __fmul_rn(v.w, k));
+}
+__device__ __forceinline__ float4 add4(const float4& a, const float4& b) {
+    return make_float4(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z), __fadd_rn(a.w, b.w));
+}
+
+struct RUCtx {
+    OptScalars h;
+    int kind;
+    float* param; float* grad; float* state0; float* state1; uint16_t* shadow;
+};
+
+__device__ __forceinline__ void ru_update(const RUCtx& c, int idx, float4 g) {
+    float4 p = *reinterpret_cast<float4*>(c.param + idx);
+    float4 s0 = *reinterpret_cast<float4*>(c.state0 + idx);
+    float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool two = (c.kind != 1);
+    if (two) s1 = *reinterpret_cast<float4*>(c.state1 + idx);
+    opt_apply(c.kind, c.h, g.x, p.x, s0.x, s1.x);
+    opt_apply(c.kind, c.h, g.y, p.y, s0.y, s1.y);
+    opt_apply(c.kind, c.h, g.z, p.z, s0.z, s1.z);
+    opt_apply(c.kind, c.h, g.w, p.w, s0.w, s1.w);
+    *reinterpret_cast<float4*>(c.param + idx) = p;
+    *reinterpret_cast<float4*>(c.state0 + idx) = s0;
+    if (two) *reinterpret_cast<float4*>(c.state1 + idx) = s1;
+    *reinterpret_cast<float4*>(c.grad + idx) = g;     // param.grad == mean over ranks, like train.py:39
+    if (c.shadow) {
+        uint2 packed;
+        packed.x = (uint32_t)f32_to_bf16_rn(p.x) | ((uint32_t)f32_to_bf16_rn(p.y) << 16);
+        packed.y = (uint32_t)f32_to_bf16_rn(p.z) | ((uint32_t)f32_to_bf16_rn(p.w) << 16);
+        *reinterpret_cast<uint2*>(c.shadow + idx) = packed;
+    }
+}
+
+// spin until *flag >= gen (generation numbers only grow); bounded so a dead peer is an error, not a hang
+__device__ __forceinline__ bool ru_wait(const uint32_t* flag, uint32_t gen) {
+    unsigned spins = 0;
+    while ((int)(ld_acquire_sys(flag) - gen) < 0) {
+        if (++spins > RU_SPIN_LIMIT) return false;
+        __nanosleep(20);
+    }
+    return true;
 }
 
 __global__ void __launch_bounds__(RU_NT) reduce_update_kernel(RUArgs a) {
@@ -95,22 +157,32 @@ __global__ void __launch_bounds__(RU_NT) reduce_update_kernel(RUArgs a) {
     const int tid = threadIdx.x;
     const int off = blockIdx.x * a.slice;                 // offset inside the bucket
     const int n_here = min(a.slice, a.count - off);       // multiple of 4 (buckets are 128-aligned)
+    const int chunks = (n_here + RU_CHUNK - 1) / RU_CHUNK;  // 1024-float chunks, one float4 per thread each
     const uint32_t gen = a.step_counter[0] + 1u;          // constant for the whole step
     const int world = a.comm.world;
-    const bool active = tid * 4 < n_here;
-    const int idx = a.start + off + tid * 4;              // arena index of this thread's float4
+    const int base_idx = a.start + off + tid * 4;         // arena index of this thread's float4 in chunk 0
     if (tid == 0) sTimeout = 0;
 
-    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-    // ---- A: local gradient for this slice ----
-    if (a.partials) {
-        // slice == RU_PSLICE: thread (o = tid%32, pg = tid/32) sums rows pg, pg+8, ... ; then 8 -> 1
-        const int o = tid & 31, pg = tid >> 5;
+    RUCtx cx;
+    cx.kind = a.opt_kind; cx.param = a.param; cx.grad = a.grad; cx.state0 = a.state0; cx.state1 = a.state1;
+    cx.shadow = a.shadow;
+    cx.h.lr = a.hyper[0]; cx.h.h0 = a.hyper[1]; cx.h.h1 = a.hyper[2]; cx.h.h2 = a.hyper[3]; cx.h.wd = a.hyper[4];
+    cx.h.c0 = cx.h.c1 = 1.f;
+    if (a.opt_kind == 2) {
+        const float t = (float)gen;
+        cx.h.c0 = 1.f / (1.f - powf(cx.h.h0, t));
+        cx.h.c1 = rsqrtf(1.f - powf(cx.h.h1, t));
+    }
+
+    // ---- A: (optional) sum the partial-gradient rows of this 32-float slice, fixed order ----
+    const bool from_rows = a.partials != nullptr;
+    if (from_rows) {
+        const int o = tid & 31, pg = tid >> 5;            // thread (o, pg) sums rows pg, pg+8, ...; then 8 -> 1
         float s = 0.f;
         if (o < n_here) {
             const float* src = a.partials + off + o;
             int r = pg;
-            for (; r + 56 < a.n_partials; r += 64) {          // 8 independent loads in flight, added in row order
+            for (; r + 56 < a.n_partials; r += 64) {      // 8 independent loads in flight, added in row order
                 float t[8];
 #pragma unroll
                 for (int u = 0; u < 8; ++u) t[u] = __ldcg(src + (long)(r + 8 * u) * a.partial_stride);
@@ -128,95 +200,133 @@ __global__ void __launch_bounds__(RU_NT) reduce_update_kernel(RUArgs a) {
             sSlice[tid] = t;
         }
         __syncthreads();
-        if (active) g = *reinterpret_cast<const float4*>(sSlice + tid * 4);
-    } else if (active) {
-        g = *reinterpret_cast<const float4*>(a.grad + idx);
     }
+    auto active = [&](int c) { return c * RU_CHUNK + tid * 4 < n_here; };
+    auto local_g = [&](int c) -> float4 {
+        return from_rows ? *reinterpret_cast<const float4*>(sSlice + tid * 4)
+                         : *reinterpret_cast<const float4*>(a.grad + base_idx + c * RU_CHUNK);
+    };
 
-    // ---- B: one-shot all-reduce over peer memory ----
-    if (world > 1) {
+    if (world == 1) {
+        for (int c = 0; c < chunks; ++c)
+            if (active(c)) ru_update(cx, base_idx + c * RU_CHUNK, local_g(c));
+    } else {
+        // ---- B: all-reduce over peer memory ----
         const int parity = gen & 1u;
-        const long sidx = (long)parity * a.comm.arena_len + idx;
-        if (active) {
-            float* my_stage = nullptr;
+        const long pbase = (long)parity * a.comm.arena_len;
+        const int rank = a.comm.rank;
+        // pointer tables are read with compile-time indices (run-time indexing of kernel parameters
+        // compiles to slow indexed constant loads)
+        float* my_stage = nullptr;
+        uint32_t* my_flags = nullptr;
 #pragma unroll
-            for (int r = 0; r < 8; ++r)
-                if (r == a.comm.rank) my_stage = a.comm.stage[r];
-            *reinterpret_cast<float4*>(my_stage + sidx) = g;
-            __threadfence_system();
-        }
+        for (int r = 0; r < 8; ++r)
+            if (r == rank) { my_stage = a.comm.stage[r]; my_flags = a.comm.flags[r]; }
+        for (int c = 0; c < chunks; ++c)
+            if (active(c)) *reinterpret_cast<float4*>(my_stage + pbase + base_idx + c * RU_CHUNK) = local_g(c);   // publish
+        __threadfence_system();
         __syncthreads();
         const int slot = (a.start + off) / RU_FLAG_GRAIN;
-        if (tid < world && tid != a.comm.rank) {
-            // publish to peer `tid`, then wait for peer `tid`'s publication of the same slice.
-            // (pointer tables are read with compile-time indices: run-time indexing of kernel
-            // parameters compiles to slow indexed constant loads)
-            uint32_t* peer_flags = nullptr;
-            uint32_t* my_flags = nullptr;
-#pragma unroll
-            for (int r = 0; r < 8; ++r) {
-                if (r == tid) peer_flags = a.comm.flags[r];
-                if (r == a.comm.rank) my_flags = a.comm.flags[r];
-            }
-            st_release_sys(peer_flags + (long)a.comm.rank * a.comm.max_slices + slot, gen);
-            const uint32_t* mine = my_flags + (long)tid * a.comm.max_slices + slot;
-            unsigned spins = 0;
-            while ((int)(ld_acquire_sys(mine) - gen) < 0) {
-                if (++spins > RU_SPIN_LIMIT) { sTimeout = 1; break; }   // dead peer: error, not a hang
-                __nanosleep(20);
-            }
-        }
-        __syncthreads();
-        if (sTimeout) {
-            if (tid == 0) atomicExch(a.step_counter + 2, 1u);
-            return;   // leave parameters untouched; the host sees the error flag
-        }
-        if (active) {
-            float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float inv = __fdiv_rn(1.f, (float)world);
+        auto sum_ranks = [&](int c) -> float4 {           // rank order: identical on every rank
+            const long sidx = pbase + base_idx + c * RU_CHUNK;
+            const float4 own = local_g(c);
             float4 v[8];
 #pragma unroll
-            for (int r = 0; r < 8; ++r)                  // all peer loads in flight together
-                if (r < world && r != a.comm.rank) v[r] = ld_volatile_f4(a.comm.stage[r] + sidx);
+            for (int r = 0; r < 8; ++r)                   // all peer loads in flight together
+                if (r < world && r != rank) v[r] = ld_volatile_f4(a.comm.stage[r] + sidx);
+            float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int r = 0; r < 8; ++r) {                // rank order, identical on every rank
-                if (r < world) {
-                    const float4 t = (r == a.comm.rank) ? g : v[r];
-                    sum.x += t.x; sum.y += t.y; sum.z += t.z; sum.w += t.w;
+            for (int r = 0; r < 8; ++r) {
+                if (r < world) sum = add4(sum, (r == rank) ? own : v[r]);
+            }
+            return sum;
+        };
+
+        if (a.comm.algo == 0) {
+            // ---- one-shot: everyone reads everyone (latency-optimal; (world-1) x bytes in per rank) ----
+            if (tid < world && tid != rank) {
+                uint32_t* peer_flags = nullptr;
+#pragma unroll
+                for (int r = 0; r < 8; ++r)
+                    if (r == tid) peer_flags = a.comm.flags[r];
+                st_release_sys(peer_flags + (long)rank * a.comm.max_slices + slot, gen);
+                if (!ru_wait(my_flags + (long)tid * a.comm.max_slices + slot, gen)) sTimeout = 1;
+            }
+            __syncthreads();
+            if (sTimeout) {
+                if (tid == 0) atomicExch(a.step_counter + 2, 1u);
+                return;   // leave parameters untouched; the host sees the error flag
+            }
+            for (int c = 0; c < chunks; ++c) {
+                if (active(c)) {
+                    const float4 s = sum_ranks(c);
+                    ru_update(cx, base_idx + c * RU_CHUNK, scale4(s, inv));
                 }
             }
-            const float inv = 1.f / (float)world;
-            g = make_float4(sum.x * inv, sum.y * inv, sum.z * inv, sum.w * inv);
-        }
-    }
-
-    // ---- C: optimizer ----
-    if (active) {
-        OptScalars h;
-        h.lr = a.hyper[0]; h.h0 = a.hyper[1]; h.h1 = a.hyper[2]; h.h2 = a.hyper[3]; h.wd = a.hyper[4];
-        h.c0 = h.c1 = 1.f;
-        if (a.opt_kind == 2) {
-            const float t = (float)gen;
-            h.c0 = 1.f / (1.f - powf(h.h0, t));
-            h.c1 = rsqrtf(1.f - powf(h.h1, t));
-        }
-        float4 p = *reinterpret_cast<float4*>(a.param + idx);
-        float4 s0 = *reinterpret_cast<float4*>(a.state0 + idx);
-        float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f);
-        const bool two = (a.opt_kind != 1);
-        if (two) s1 = *reinterpret_cast<float4*>(a.state1 + idx);
-        opt_apply(a.opt_kind, h, g.x, p.x, s0.x, s1.x);
-        opt_apply(a.opt_kind, h, g.y, p.y, s0.y, s1.y);
-        opt_apply(a.opt_kind, h, g.z, p.z, s0.z, s1.z);
-        opt_apply(a.opt_kind, h, g.w, p.w, s0.w, s1.w);
-        *reinterpret_cast<float4*>(a.param + idx) = p;
-        *reinterpret_cast<float4*>(a.state0 + idx) = s0;
-        if (two) *reinterpret_cast<float4*>(a.state1 + idx) = s1;
-        *reinterpret_cast<float4*>(a.grad + idx) = g;     // param.grad == mean over ranks, like train.py:39
-        if (a.shadow) {
-            uint2 packed;
-            packed.x = (uint32_t)f32_to_bf16_rn(p.x) | ((uint32_t)f32_to_bf16_rn(p.y) << 16);
-            packed.y = (uint32_t)f32_to_bf16_rn(p.z) | ((uint32_t)f32_to_bf16_rn(p.w) << 16);
-            *reinterpret_cast<uint2*>(a.shadow + idx) = packed;
+        } else {
+            // ---- two-shot (algo 1) / NVLS (algo 2): slice j is reduced by ONE owner rank, which then
+            //      hands the sum to every peer.  Bytes per rank ~2(world-1)/world x bucket; with NVLS the
+            //      switch does the reduction (multimem.ld_reduce) and the broadcast (multimem.st).
+            //      One producer per slice also makes the result identical on all ranks by construction.
+            const int owner = (int)(blockIdx.x % (unsigned)world);
+            uint32_t* flags2_mine = my_flags + 8l * a.comm.max_slices;        // [slot], written by the owner
+            const long landing = 2l * a.comm.arena_len;                        // reduced slices land here
+            if (rank != owner) {
+                if (tid == 0) {
+                    uint32_t* owner_flags = nullptr;
+#pragma unroll
+                    for (int r = 0; r < 8; ++r)
+                        if (r == owner) owner_flags = a.comm.flags[r];
+                    st_release_sys(owner_flags + (long)rank * a.comm.max_slices + slot, gen);   // "my slice is up"
+                    if (!ru_wait(flags2_mine + slot, gen)) sTimeout = 1;                          // "the sum is here"
+                }
+                __syncthreads();
+                if (sTimeout) {
+                    if (tid == 0) atomicExch(a.step_counter + 2, 1u);
+                    return;
+                }
+                for (int c = 0; c < chunks; ++c) {
+                    if (active(c)) {
+                        const float4 t = ld_volatile_f4(my_stage + landing + base_idx + c * RU_CHUNK);
+                        ru_update(cx, base_idx + c * RU_CHUNK, scale4(t, inv));
+                    }
+                }
+            } else {
+                if (tid < world && tid != rank)
+                    if (!ru_wait(my_flags + (long)tid * a.comm.max_slices + slot, gen)) sTimeout = 1;
+                __syncthreads();
+                if (sTimeout) {
+                    if (tid == 0) atomicExch(a.step_counter + 2, 1u);
+                    return;
+                }
+                for (int c = 0; c < chunks; ++c) {
+                    if (active(c)) {
+                        const int idx = base_idx + c * RU_CHUNK;
+                        float4 s;
+                        if (a.comm.algo == 2) {
+                            s = multimem_ld_reduce_f4(a.comm.mc_stage + pbase + idx);       // in-switch sum of all ranks
+                            multimem_st_f4(a.comm.mc_stage + landing + idx, s);             // in-switch broadcast
+                        } else {
+                            s = sum_ranks(c);
+#pragma unroll
+                            for (int r = 0; r < 8; ++r)          // push the sum into every peer's landing area
+                                if (r < world && r != rank)
+                                    *reinterpret_cast<float4*>(a.comm.stage[r] + landing + idx) = s;
+                        }
+                        ru_update(cx, idx, scale4(s, inv));
+                    }
+                }
+                __threadfence_system();
+                __syncthreads();
+                if (tid < world && tid != rank) {
+                    uint32_t* peer_flags = nullptr;
+#pragma unroll
+                    for (int r = 0; r < 8; ++r)
+                        if (r == tid) peer_flags = a.comm.flags[r];
+                    st_release_sys(peer_flags + 8l * a.comm.max_slices + slot, gen);
+                }
+            }
         }
     }
 
@@ -253,12 +363,19 @@ extern "C" int b200dp_reduce_update(float* param, float* grad, float* state0, fl
     if (comm) {
         a.comm = *comm;
         B200DP_REQUIRE(comm->world >= 1 && comm->world <= 8, "world size 1..8");
-        B200DP_REQUIRE(comm->algo == 0, "only the one-shot algorithm is built so far");
+        B200DP_REQUIRE(comm->algo >= 0 && comm->algo <= 2, "algo: 0 one-shot, 1 two-shot, 2 NVLS multimem");
+        B200DP_REQUIRE(comm->algo != 2 || comm->mc_stage != nullptr, "NVLS needs the multicast alias of the staging block");
         B200DP_REQUIRE(comm->world == 1 || (start + count) / RU_FLAG_GRAIN <= comm->max_slices, "flag block too small");
     } else {
         a.comm.world = 1; a.comm.rank = 0;
     }
-    a.slice = partials ? RU_PSLICE : RU_SLICE;
+    if (partials) {
+        a.slice = RU_PSLICE;
+    } else {
+        const int per_cta = (count + RU_MAX_CTAS - 1) / RU_MAX_CTAS;
+        a.slice = (per_cta + RU_CHUNK - 1) / RU_CHUNK * RU_CHUNK;
+        if (a.slice < RU_CHUNK) a.slice = RU_CHUNK;
+    }
     const int grid = (count + a.slice - 1) / a.slice;
     reduce_update_kernel<<<grid, RU_NT, 0, (cudaStream_t)s>>>(a);
     B200DP_CHECK(cudaGetLastError());

@@ -168,12 +168,18 @@ int b200dp_conv_bwd_noalloc(const void* x, int in_is_u8, float mean, float std, 
  * bucket launch of a step (last_bucket != 0) advances the generation. */
 typedef struct {
     int world, rank;
-    int algo;                 /* 0 one-shot, 1 two-shot, 2 NVLS multimem */
-    float* stage[8];          /* every rank's staging base (peer-mapped), [2 parities][arena_len] */
-    uint32_t* flags[8];       /* every rank's flag block (peer-mapped) */
-    float* mc_stage;          /* multicast alias of stage (NVLS) or NULL */
+    int algo;                 /* 0 one-shot: every rank reads every peer's slice (latency regime);
+                                 1 two-shot: slice j is summed by rank j%world, which pushes the sum to all;
+                                 2 NVLS: as two-shot, but the NVSwitch reduces (multimem.ld_reduce) and
+                                   broadcasts (multimem.st) through the multicast alias */
+    float* stage[8];          /* every rank's staging base (peer-mapped):
+                                 [2 parities][arena_len] published slices, then [arena_len] landing area
+                                 for reduced slices (two-shot / NVLS) => 3*arena_len floats */
+    uint32_t* flags[8];       /* every rank's flag block (peer-mapped): [8][max_slices] "slice published by
+                                 rank r", then [max_slices] "reduced slice delivered" => 9*max_slices words */
+    float* mc_stage;          /* multicast alias of the staging block (NVLS) or NULL */
     int arena_len;            /* floats per parity buffer */
-    int max_slices;           /* flag slots per source rank */
+    int max_slices;           /* flag slots per source rank (arena_len / 32) */
 } b200dp_comm;
 
 int b200dp_reduce_update(float* param, float* grad, float* state0, float* state1, uint16_t* shadow_bf16,

@@ -15,7 +15,8 @@ def train_native(ctx, cfg):
     torch.manual_seed(cfg["seed"])
     b = cfg["per_rank_batch"]
     st = NativeStepper(ctx, MNIST_LENET, OptHyper(cfg["opt"], lr=cfg["lr"]), batch=b, loss_mode="xent",
-                       graph=cfg["graph"], overlap=cfg["overlap"], dtype=cfg.get("dtype", "fp32"))
+                       graph=cfg["graph"], overlap=cfg["overlap"], dtype=cfg.get("dtype", "fp32"),
+                       algo=cfg.get("algo", "auto"))
     g = torch.Generator().manual_seed(77)
     n_batches = cfg["n_batches"]
     gx = torch.randint(0, 256, (n_batches, ctx.world_size * b, 1, 28, 28), dtype=torch.uint8, generator=g)
@@ -36,7 +37,7 @@ def train_native(ctx, cfg):
     div = st.replica_divergence()
     lt = torch.tensor(losses, device=ctx.device)
     dist.all_reduce(lt)                        # mean over ranks of per-rank mean loss == global-batch mean
-    out = {"div": div, "losses": (lt / ctx.world_size).tolist(),
+    out = {"div": div, "transport": st.comm.transport, "multicast": bool(st.comm.multicast_ptr), "losses": (lt / ctx.world_size).tolist(),
            "params": {k: v.detach().cpu().clone() for k, v in st.model.state_dict().items()},
            "gen": int(st.step_counter[0])}
     if ctx.rank == 0:

@@ -40,12 +40,14 @@ def _single_gpu_reference(cfg, world):
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
-@pytest.mark.parametrize("opt,lr", [("adadelta", 0.1), ("sgd", 0.05)])
-def test_p2p_matches_global_batch(tmp_path, world, opt, lr):
+@pytest.mark.parametrize("opt,lr,algo", [("adadelta", 0.1, "oneshot"), ("sgd", 0.05, "oneshot"),
+                                         ("adadelta", 0.1, "twoshot"), ("sgd", 0.05, "nvls")])
+def test_p2p_matches_global_batch(tmp_path, world, opt, lr, algo):
+    """``nvls`` falls back to two-shot (with a warning) where the box has no multicast support."""
     _need(world)
     from b200dp.parallel import launch
     cfg = {"seed": 5, "per_rank_batch": 64, "n_batches": 3, "steps": 12, "opt": opt, "lr": lr, "graph": True,
-           "overlap": True, "out": str(tmp_path), "tag": "a"}
+           "overlap": True, "out": str(tmp_path), "tag": "a", "algo": algo}
     launch.spawn(train_native, cfg, world, backend="nccl", use_cuda=True, port=0)
     got = torch.load(os.path.join(tmp_path, "native_a.pt"))
     ref_losses, ref_params = _single_gpu_reference(cfg, world)
