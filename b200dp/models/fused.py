@@ -217,6 +217,7 @@ class NativeStepper:
         self._static_x: Optional[torch.Tensor] = None
         self._static_y: Optional[torch.Tensor] = None
         self._warm = 0
+        self._comm_off = False        # measurement aid: see set_comm_enabled
         self.launches_per_step = 11   # 5 fwd + 3 bwd + 3 reduce/update
 
     # ---- optimizer scalars live on the device so graph replays see scheduler changes ----
@@ -241,7 +242,7 @@ class NativeStepper:
                              net.partials if is_conv else None, net.cur_partials if is_conv else 0,
                              net.partial_stride if is_conv else 0, opt.hyper.code(), self.hyper_dev,
                              self.step_counter, bucket_index == 2,
-                             self.comm.struct_for(b.numel * 4) if self.comm else None)
+                             self.comm.struct_for(b.numel * 4) if (self.comm and not self._comm_off) else None)
 
     def _step_body(self, x: torch.Tensor, y: torch.Tensor) -> None:
         main = torch.cuda.current_stream(self.device)
@@ -295,6 +296,14 @@ class NativeStepper:
         self._static_y.copy_(y)
         self._graphs[("static",)].replay()
         return self.net.loss
+
+    def set_comm_enabled(self, on: bool) -> None:
+        """Measurement aid for the exposed-communication number: with ``on=False`` the reduce+update
+        launches skip the cross-rank exchange (each rank applies its local gradient), everything else
+        stays the same.  Replicas diverge while it is off — use only at the end of a benchmark."""
+        self._comm_off = not on
+        self._graphs.clear()
+        self._static_x = self._static_y = None
 
     # ---- eval ----------------------------------------------------------------------
     def eval_batch(self, x: torch.Tensor, y: torch.Tensor) -> None:

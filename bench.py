@@ -44,8 +44,8 @@ L2_BYTES = 126 * 1024 * 1024
 def _parse():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=300)
-    p.add_argument("--warmup", type=int, default=30)
+    p.add_argument("--steps", type=int, default=2000)
+    p.add_argument("--warmup", type=int, default=200)
     p.add_argument("--impl", choices=["b200dp", "reference"], default="b200dp")
     p.add_argument("--config", choices=["lenet_b256", "strong4096", "wide_cifar"], default="lenet_b256")
     p.add_argument("--optimizer", default="adadelta")
@@ -129,10 +129,12 @@ def run_own(args):
         sy.copy_(pool_y[j], non_blocking=True)
         return stepper.train_step(sx, sy)
 
+    # clocks are sampled from before the warm-up until after the timed region (the timed region alone
+    # can be shorter than one nvidia-smi sampling period)
+    sampler = ClockSampler(local, period_ms=20).start() if rank == 0 else None
     for i in range(W):
         dev_step(i)
     _sync_all()
-    sampler = ClockSampler(local).start() if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(K):
@@ -177,6 +179,21 @@ def run_own(args):
     loss_e2e = float(loss_ring[W + K - 1])
     div = stepper.replica_divergence()
 
+    # ---- exposed communication per step: same device-timed loop with the cross-rank exchange elided ----
+    exposed_us = None
+    if world > 1:
+        stepper.set_comm_enabled(False)
+        for i in range(W):
+            dev_step(i)
+        _sync_all()
+        e0.record()
+        for i in range(K):
+            dev_step(W + i)
+        e1.record()
+        _sync_all()
+        ms_nocomm = _max_ranks(e0.elapsed_time(e1), dev)
+        exposed_us = (ms - ms_nocomm) / K * 1e3
+
     if rank == 0:
         imgs = batch * world * K
         out = {
@@ -201,6 +218,7 @@ def run_own(args):
             "gpu_launches": stepper.launches_per_step * K,
             "final_loss": {"device_path": loss_dev, "e2e_path": loss_e2e},
             "replica_divergence": div,
+            "exposed_comm_us_per_step": exposed_us,
             "native_lib": os.path.relpath(native.lib_path(), ROOT),
         }
         print(json.dumps(out), flush=True)
@@ -262,7 +280,7 @@ def run_reference(args):
     optimizer = torch.optim.Adadelta(model.parameters(), lr=0.1)               # train.py:99
     ref_args = types.SimpleNamespace(log_interval=15, dry_run=False)           # train.py defaults
     loader = _RefLoader(xs, ys, batch, W, K)
-    sampler = ClockSampler(local).start() if rank == 0 else None
+    sampler = ClockSampler(local, period_ms=20).start() if rank == 0 else None
     with contextlib.redirect_stdout(io.StringIO()):                            # keep its rank-0 log lines off stdout
         ref_train.train(ref_args, model, local, loader, optimizer, 1)          # the reference's own loop
     loader.e1.record()

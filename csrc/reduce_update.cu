@@ -26,7 +26,8 @@ namespace b200dp {
 
 constexpr int RU_NT = 256;
 constexpr int RU_CHUNK = 1024;        // floats per CTA iteration (float4 per thread)
-constexpr int RU_MAX_CTAS = 148 * 8;  // large buckets: at most this many CTAs, each looping over chunks
+constexpr int RU_MAX_CTAS = 148 * 2;  // = resident CTAs (2 per SM at this register count): one handshake wave,
+                                      // larger buckets loop over chunks inside each CTA
 constexpr int RU_PSLICE = 32;         // floats per CTA when partial rows are pre-reduced
 constexpr int RU_FLAG_GRAIN = 32;     // one flag slot per 32 arena floats
 constexpr unsigned RU_SPIN_LIMIT = 1u << 28;
@@ -150,7 +151,7 @@ __device__ __forceinline__ bool ru_wait(const uint32_t* flag, uint32_t gen) {
     return true;
 }
 
-__global__ void __launch_bounds__(RU_NT) reduce_update_kernel(RUArgs a) {
+__global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
     __shared__ float sRed[8][RU_PSLICE];
     __shared__ __align__(16) float sSlice[RU_PSLICE];
     __shared__ int sTimeout;
