@@ -41,7 +41,8 @@ class NativeLeNet:
     """Buffers + kernel launch sequences for one model replica on one GPU."""
 
     def __init__(self, cfg: LeNetConfig, batch: int, device: torch.device, *, loss_mode: str = "ref",
-                 spec: ImageSpec = MNIST_SPEC, module: Optional[LeNet] = None, tc: bool = False):
+                 spec: ImageSpec = MNIST_SPEC, module: Optional[LeNet] = None, tc: bool = False,
+                 conv_tc: Optional[bool] = None):
         """``tc=True`` routes the five GEMM-shaped layers (conv3, FC.0 and their backward, FC.2's weight
         gradient) through the tcgen05/TMEM/TMA tf32 kernel; ``tc=False`` keeps everything in exact fp32
         on CUDA cores.  In tc mode the GEMM operand buffers carry one extra column of ones (the bias
@@ -49,6 +50,11 @@ class NativeLeNet:
         native.load()
         self.cfg, self.B, self.device, self.spec = cfg, int(batch), torch.device(device), spec
         self.tc = bool(tc)
+        # convolutions: tcgen05 implicit GEMM (csrc/tc_conv.cu) or CUDA cores (conv_fwd.cu / conv_bwd.cu).
+        # The fused CUDA-core backward only exists for the reference geometry; the wide model needs tc.
+        self.conv_tc = (cfg.width_mult > 1) if conv_tc is None else bool(conv_tc)
+        if cfg.width_mult > 1 and not self.conv_tc:
+            raise ValueError("the wide model's convolution backward runs on the tensor-core kernels only")
         self.loss_mode = _LOSS_MODES[loss_mode]
         self.module = module if module is not None else LeNet(cfg)
         self.module.to(self.device)
@@ -89,7 +95,9 @@ class NativeLeNet:
         self.dp2 = torch.empty(B, c.c2 * 25, **f32)
         self.ticket = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.eval_acc = torch.zeros(2, dtype=torch.float64, device=self.device)
-        self.n_partials = native.conv_bwd_num_partials(self.dims(B))   # rows allocated (full batch)
+        self.g1 = torch.empty(B, c.c1, 14, 14, **f32) if self.conv_tc else None
+        self._num_partials = native.tc_conv_wgrad_num_partials if self.conv_tc else native.conv_bwd_num_partials
+        self.n_partials = self._num_partials(self.dims(B))   # rows allocated (full batch)
         self.cur_partials = self.n_partials    # rows the last backward actually wrote (fewer on a ragged batch)
         self.partial_stride = self.bucket_conv.numel
         # scratch: one partial-gradient row per conv-backward CTA (zeroed once: padding columns stay 0)
@@ -109,10 +117,10 @@ class NativeLeNet:
         b = x.shape[0]
         assert b <= self.B and x.is_contiguous() and y.dtype == torch.int64
         d, w = self.dims(b), self.w
-        native.conv1_fwd(x, w["ConvNet.1.weight"], w["ConvNet.1.bias"], self.p1, self.idx1 if train else None,
-                         d, self.spec.mean, self.spec.std)
-        native.conv2_fwd(self.p1, w["ConvNet.4.weight"], w["ConvNet.4.bias"], self.p2,
-                         self.idx2 if train else None, d)
+        conv1, conv2 = (native.tc_conv1_fwd, native.tc_conv2_fwd) if self.conv_tc else (native.conv1_fwd, native.conv2_fwd)
+        conv1(x, w["ConvNet.1.weight"], w["ConvNet.1.bias"], self.p1, self.idx1 if train else None,
+              d, self.spec.mean, self.spec.std)
+        conv2(self.p1, w["ConvNet.4.weight"], w["ConvNet.4.bias"], self.p2, self.idx2 if train else None, d)
         c = self.cfg
         k3 = c.c2 * 25
         if self.tc:
@@ -174,9 +182,17 @@ class NativeLeNet:
             if on_bucket:
                 on_bucket(1)
         ow1, ob1, ow2, ob2 = self.conv_offsets
-        self.cur_partials = native.conv_bwd_num_partials(d)
-        native.conv_bwd(x, self.spec.mean, self.spec.std, self.p1, self.idx1, self.p2, self.idx2, self.dp2,
-                        w["ConvNet.4.weight"], self.partials, self.partial_stride, ow1, ob1, ow2, ob2, d)
+        self.cur_partials = self._num_partials(d)
+        if self.conv_tc:
+            ld_p2 = self.ld_p2 or k3
+            native.tc_conv2_dgrad(self.dp2, self.p2, self.idx2, w["ConvNet.4.weight"], self.p1, self.g1, d)
+            native.tc_conv_wgrad(2, self.p1, 0.0, 1.0, self.dp2, self.p2, ld_p2, self.idx2, self.partials,
+                                 self.partial_stride, ow2, ob2, d)
+            native.tc_conv_wgrad(1, x, self.spec.mean, self.spec.std, self.g1, None, 0, self.idx1, self.partials,
+                                 self.partial_stride, ow1, ob1, d)
+        else:
+            native.conv_bwd(x, self.spec.mean, self.spec.std, self.p1, self.idx1, self.p2, self.idx2, self.dp2,
+                            w["ConvNet.4.weight"], self.partials, self.partial_stride, ow1, ob1, ow2, ob2, d)
         if on_bucket:
             on_bucket(2)
 
@@ -190,7 +206,7 @@ class NativeStepper:
 
     def __init__(self, ctx, cfg: LeNetConfig, hyper: OptHyper, *, batch: int, loss_mode: str = "ref",
                  spec: ImageSpec = MNIST_SPEC, algo: str = "auto", graph: bool = True, overlap: bool = True,
-                 dtype: str = "auto", module: Optional[LeNet] = None):
+                 dtype: str = "auto", module: Optional[LeNet] = None, conv: str = "auto"):
         self.ctx, self.cfg = ctx, cfg
         self.device = ctx.device
         if dtype not in ("auto", "fp32", "tf32", "bf16"):
@@ -200,8 +216,10 @@ class NativeStepper:
             # kernels finish sooner than one tcgen05 pipeline fill; the tensor-core path wins for the wide model
             dtype = "tf32" if cfg.width_mult > 1 else "fp32"
         self.dtype = "fp32" if dtype == "fp32" else "tf32"      # "bf16" is accepted as a request for the tensor-core path
+        if conv not in ("auto", "simt", "tc"):
+            raise ValueError(f"unknown conv mode {conv!r}")
         self.net = NativeLeNet(cfg, batch, self.device, loss_mode=loss_mode, spec=spec, module=module,
-                               tc=self.dtype != "fp32")
+                               tc=self.dtype != "fp32", conv_tc=None if conv == "auto" else conv == "tc")
         self.model = self.net.module
         self.arena = self.net.arena
         self.optimizer = FlatOptimizer(self.arena.param, self.arena.grad, hyper)
@@ -218,7 +236,7 @@ class NativeStepper:
         self._static_y: Optional[torch.Tensor] = None
         self._warm = 0
         self._comm_off = False        # measurement aid: see set_comm_enabled
-        self.launches_per_step = 11   # 5 fwd + 3 bwd + 3 reduce/update
+        self.launches_per_step = 13 if self.net.conv_tc else 11   # 5 fwd + 3 (5 with tc convs) bwd + 3 reduce/update
 
     # ---- optimizer scalars live on the device so graph replays see scheduler changes ----
     def _sync_hyper(self) -> None:

@@ -311,3 +311,30 @@ def test_ragged_batch_after_full_batch():
         assert abs(le - ln) < 5e-4 * max(1.0, abs(le)), (b, le, ln)
     for (n, a), (_, c) in zip(eager.model.state_dict().items(), nat.model.state_dict().items()):
         assert torch.allclose(a, c, atol=5e-4, rtol=5e-3), (n, (a - c).abs().max())
+
+
+@pytest.mark.parametrize("cfg_name", ["mnist_tc_conv", "wide"])
+def test_tc_conv_training_matches_eager(cfg_name):
+    """Full steps with the tcgen05 convolutions (and GEMMs): the wide CIFAR-shaped model, and the
+    reference model with conv='tc'."""
+    from b200dp.data.synthetic import CIFAR_SPEC, MNIST_SPEC
+    from b200dp.engine import EagerStepper
+    from b200dp.models.fused import NativeStepper
+    from b200dp.optim.flat import OptHyper
+    from b200dp.parallel.launch import RankContext
+    torch.manual_seed(10)
+    dev = torch.device("cuda", 0)
+    ctx = RankContext(0, 1, 0, dev, "nccl")
+    cfg, spec = (CIFAR_WIDE_LENET, CIFAR_SPEC) if cfg_name == "wide" else (MNIST_LENET, MNIST_SPEC)
+    eager = EagerStepper(ctx, cfg, OptHyper("sgd", lr=0.02), loss_mode="xent", spec=spec)
+    nat = NativeStepper(ctx, cfg, OptHyper("sgd", lr=0.02), batch=64, loss_mode="xent", spec=spec, graph=True,
+                        dtype="tf32", conv="tc")
+    nat.model.load_state_dict(eager.model.state_dict())
+    shape = (64, cfg.in_ch, cfg.in_hw, cfg.in_hw)
+    xs = [torch.randint(0, 256, shape, dtype=torch.uint8, device=dev) for _ in range(2)]
+    ys = [torch.randint(0, 10, (64,), device=dev) for _ in range(2)]
+    for i in range(6):
+        le, ln = float(eager.train_step(xs[i % 2], ys[i % 2])), float(nat.train_step(xs[i % 2], ys[i % 2]))
+        assert abs(le - ln) < 1e-2 * max(1.0, abs(le)), (i, le, ln)
+    for (n, a), (_, b) in zip(eager.model.state_dict().items(), nat.model.state_dict().items()):
+        assert torch.allclose(a, b, atol=5e-3, rtol=5e-2), (n, (a - b).abs().max())
