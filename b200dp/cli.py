@@ -55,6 +55,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--allreduce-algo", choices=["auto", "oneshot", "twoshot", "nvls"], default="auto")
     p.add_argument("--no-overlap", action="store_true", help="reduce after backward, not during it")
     p.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
+    p.add_argument("--no-pump", action="store_true",
+                   help="drive every step from Python instead of the native C++ step pump")
     p.add_argument("--eager", action="store_true", help="torch eager kernels instead of the native ones")
     p.add_argument("--global-eval", action="store_true",
                    help="sum eval metrics over ranks (the reference prints rank 0's shard only)")

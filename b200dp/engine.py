@@ -90,12 +90,67 @@ class Trainer:
     """Epoch loops around a stepper (reference ``train`` / ``test``)."""
 
     def __init__(self, ctx: RankContext, stepper, logger: RankLogger, *, log_interval: int = 15,
-                 dry_run: bool = False, global_eval: bool = False):
+                 dry_run: bool = False, global_eval: bool = False, no_pump: bool = False):
         self.ctx, self.stepper, self.log = ctx, stepper, logger
         self.log_interval, self.dry_run, self.global_eval = log_interval, dry_run, global_eval
         self.global_step = 0
+        self.no_pump = no_pump
+        self._pumps = {}
+        self._loss_ring = None
+
+    def _pump_for(self, loader):
+        """The native step pump for (stepper, loader), when the combination supports it: native stepper with
+        CUDA graphs, raw uint8 samples streamed to a CUDA device."""
+        st = self.stepper
+        if not (hasattr(st, "make_pump") and getattr(st, "use_graph", False) and not self.no_pump):
+            return None
+        if not (isinstance(loader, PinnedRingLoader) and loader.fmt == "u8" and loader.device is not None
+                and loader.device.type == "cuda" and loader.batch_size == st.net.B):
+            return None
+        key = id(loader)
+        if key not in self._pumps:
+            self._pumps[key] = st.make_pump(loader.images, loader.targets, loader.batch_size)
+        return self._pumps[key]
+
+    def _train_epoch_pumped(self, pump, loader, epoch: int) -> Optional[float]:
+        """Same epoch as the Python loop below — same sample order, same log lines — but the per-step host
+        work runs in the C++ pump, one ctypes call per ``log_interval`` steps.  The log line of a chunk is
+        printed once its first step has finished, while the rest of the chunk is still queued."""
+        order = loader._order().contiguous()
+        loader.epoch += 1
+        B, n_batches = loader.batch_size, len(loader)
+        n_full = (loader.stop - loader.start) // B
+        run_ragged = n_full < n_batches
+        if self.dry_run and n_full >= 1:                      # train.py:56-57: one batch only
+            n_full, run_ragged = 1, False
+        if self._loss_ring is None or self._loss_ring.numel() < n_batches:
+            self._loss_ring = torch.zeros(max(n_batches, 64), dtype=torch.float32).pin_memory()
+        last = None
+        for c0 in range(0, n_full, self.log_interval):
+            n = min(self.log_interval, n_full - c0)
+            pump.run(order[c0 * B:], n, self._loss_ring[c0:])
+            self.global_step += n
+            if self.ctx.is_main:
+                pump.wait_first()
+                last = float(self._loss_ring[c0])
+                self.log.print(train_line(epoch, c0, B, len(loader.dataset), n_batches, last))
+                self.log.event(kind="train", epoch=epoch, step=self.global_step - n + 1, batch_idx=c0, loss=last)
+        if run_ragged:                                        # ragged last batch: Python path
+            idx = order[n_full * B:]
+            x = loader.images.index_select(0, idx).to(self.ctx.device)
+            y = loader.targets.index_select(0, idx).to(self.ctx.device)
+            loss = self.stepper.train_step(x, y)
+            self.global_step += 1
+            if n_full % self.log_interval == 0 and self.ctx.is_main:
+                last = float(loss.item())
+                self.log.print(train_line(epoch, n_full, len(x), len(loader.dataset), n_batches, last))
+        pump.drain()
+        return last
 
     def train_epoch(self, loader, epoch: int) -> Optional[float]:
+        pump = self._pump_for(loader)
+        if pump is not None:
+            return self._train_epoch_pumped(pump, loader, epoch)
         last = None
         n_batches = len(loader)
         for batch_idx, (data, target) in enumerate(loader):
@@ -172,7 +227,7 @@ def run(ctx: RankContext, args) -> dict:
     scheduler = StepLR(stepper.optimizer, step_size=1, gamma=args.gamma)     # train.py:101
     logger = RankLogger(ctx.is_main, getattr(args, "jsonl", None))
     trainer = Trainer(ctx, stepper, logger, log_interval=args.log_interval, dry_run=args.dry_run,
-                      global_eval=getattr(args, "global_eval", False))
+                      global_eval=getattr(args, "global_eval", False), no_pump=getattr(args, "no_pump", False))
 
     start_epoch = 1
     if getattr(args, "resume", None):

@@ -236,6 +236,7 @@ class NativeStepper:
         self._static_y: Optional[torch.Tensor] = None
         self._warm = 0
         self._comm_off = False        # measurement aid: see set_comm_enabled
+        self._pumps = []
         self.launches_per_step = 13 if self.net.conv_tc else 11   # 5 fwd + 3 (5 with tc convs) bwd + 3 reduce/update
 
     # ---- optimizer scalars live on the device so graph replays see scheduler changes ----
@@ -315,12 +316,23 @@ class NativeStepper:
         self._graphs[("static",)].replay()
         return self.net.loss
 
+    def make_pump(self, images: torch.Tensor, targets: torch.Tensor, batch: int, depth: int = 3):
+        """A native step pump (csrc/pump.cu) over the host arrays ``images`` (uint8) / ``targets``: queues whole
+        runs of steps — sample gather into a pinned ring, H2D copy, this stepper's step, loss read-back — from
+        a C++ loop.  See :class:`b200dp.data.pump.StepPump`."""
+        from ..data.pump import StepPump
+        pump = StepPump(self, images, targets, batch, depth=depth)
+        self._pumps.append(pump)
+        return pump
+
     def set_comm_enabled(self, on: bool) -> None:
         """Measurement aid for the exposed-communication number: with ``on=False`` the reduce+update
         launches skip the cross-rank exchange (each rank applies its local gradient), everything else
         stays the same.  Replicas diverge while it is off — use only at the end of a benchmark."""
         self._comm_off = not on
         self._graphs.clear()
+        for p in self._pumps:
+            p.invalidate()
         self._static_x = self._static_y = None
 
     # ---- eval ----------------------------------------------------------------------
@@ -354,6 +366,9 @@ class NativeStepper:
         return float(d.item())
 
     def close(self) -> None:
+        for p in self._pumps:
+            p.close()
+        self._pumps.clear()
         self._graphs.clear()
         if self.comm is not None:
             self.comm.close()

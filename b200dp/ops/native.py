@@ -44,6 +44,13 @@ class Comm(C.Structure):
                 ("arena_len", C.c_int), ("max_slices", C.c_int)]
 
 
+class PumpDesc(C.Structure):
+    _fields_ = [("images", C.c_void_p), ("targets", C.c_void_p), ("image_bytes", C.c_int64),
+                ("batch", C.c_int), ("depth", C.c_int),
+                ("host_x", C.c_void_p * 8), ("host_y", C.c_void_p * 8), ("graph_exec", C.c_void_p * 8),
+                ("loss_dev", C.c_void_p)]
+
+
 def lib_path() -> str:
     return _LIB_PATH
 
@@ -85,6 +92,14 @@ def load(build_if_missing: bool = True):
     lib.b200dp_symm_import.argtypes = [C.c_char_p, C.POINTER(vp)]
     lib.b200dp_symm_close.argtypes = [vp]
     lib.b200dp_enable_peer_access.argtypes = [i]
+    lib.b200dp_pump_create.argtypes = [C.POINTER(vp), C.POINTER(PumpDesc)]
+    lib.b200dp_pump_run.argtypes = [vp, vp, i, vp, vp]
+    lib.b200dp_pump_wait_first.argtypes = [vp]
+    lib.b200dp_pump_drain.argtypes = [vp]
+    lib.b200dp_pump_destroy.argtypes = [vp]
+    lib.b200dp_nvtx_push.argtypes = [C.c_char_p]
+    lib.b200dp_nvtx_push.restype = None
+    lib.b200dp_nvtx_pop.restype = None
     _lib = lib
     return lib
 
@@ -237,3 +252,37 @@ def symm_import(handle: bytes) -> int:
 
 def symm_close(ptr: int) -> None:
     check(load().b200dp_symm_close(ptr), "symm_close")
+
+
+# ---- native step pump ------------------------------------------------------------
+def pump_create(desc: PumpDesc) -> int:
+    h = C.c_void_p()
+    check(load().b200dp_pump_create(C.byref(h), C.byref(desc)), "pump_create")
+    return h.value
+
+
+def pump_run(handle: int, order: torch.Tensor, n_steps: int, loss_host: Optional[torch.Tensor]) -> None:
+    """``order``: contiguous CPU int64 sample indices (n_steps*batch of them are read);
+    ``loss_host``: pinned float32 tensor with >= n_steps elements, or None."""
+    assert order.dtype == torch.int64 and order.is_contiguous() and not order.is_cuda
+    check(load().b200dp_pump_run(handle, order.data_ptr(), n_steps, _p(loss_host), _stream()), "pump_run")
+
+
+def pump_wait_first(handle: int) -> None:
+    check(load().b200dp_pump_wait_first(handle), "pump_wait_first")
+
+
+def pump_drain(handle: int) -> None:
+    check(load().b200dp_pump_drain(handle), "pump_drain")
+
+
+def pump_destroy(handle: int) -> None:
+    check(load().b200dp_pump_destroy(handle), "pump_destroy")
+
+
+def nvtx_push(name: str) -> None:
+    load().b200dp_nvtx_push(name.encode())
+
+
+def nvtx_pop() -> None:
+    load().b200dp_nvtx_pop()

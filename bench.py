@@ -51,6 +51,7 @@ def _parse():
     p.add_argument("--optimizer", default="adadelta")
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--no-overlap", action="store_true")
+    p.add_argument("--no-pump", action="store_true", help="e2e: drive every step from Python")
     p.add_argument("--input", choices=["u8", "f32"], default="u8", help="host->device input format (e2e)")
     p.add_argument("--dtype", choices=["auto", "fp32", "tf32"], default="auto",
                    help="tf32 = tcgen05 tensor-core GEMMs on fp32 tensors; fp32 = exact CUDA-core kernels")
@@ -147,36 +148,31 @@ def run_own(args):
     loss_dev = float(stepper.net.loss)
 
     # ---- end to end through the public API: pinned host -> device every step, loss read back ----
-    n_host = max(2 * (K + W), 64) * batch
-    n_host = min(n_host, 200_000)
+    # Trainer.train_epoch is the call a user makes (b200dp.engine.run makes it once per epoch); with the
+    # native stepper it drives the C++ step pump: per step, gather into a pinned ring slot, one graph launch
+    # (H2D copies of the slot + the whole step) and a 4-byte D2H copy of the loss into a pinned array.
+    from b200dp.engine import Trainer
+    from b200dp.utils.logging import RankLogger
+    n_host = max(K, W) * batch                              # one "epoch" of the timed loader = exactly K steps
     hx = torch.randint(0, 256, (n_host, spec.channels, spec.height, spec.width), dtype=torch.uint8, generator=g)
     hy = torch.randint(0, spec.classes, (n_host,), generator=g)
-    loader = PinnedRingLoader(hx, hy, 0, n_host, batch, spec, shuffle=True, fmt=args.input, device=dev,
-                              seed=rank, drop_last=True)
-    loss_ring = torch.zeros(K + W + 8, dtype=torch.float32).pin_memory()
-
-    def e2e_epoch(n_steps, base):
-        done = 0
-        while done < n_steps:
-            for x, y in loader:
-                loss = stepper.train_step(x, y)
-                loss_ring[base + done:base + done + 1].copy_(loss, non_blocking=True)   # D2H every step
-                done += 1
-                if done >= n_steps:
-                    break
-        return done
-
-    e2e_epoch(W, 0)
+    mk = lambda n: PinnedRingLoader(hx, hy, 0, n * batch, batch, spec, shuffle=True, fmt=args.input, device=dev,  # noqa: E731
+                                    seed=rank, drop_last=True)
+    warm_loader, loader = mk(W), mk(K)
+    trainer = Trainer(ctx, stepper, RankLogger(False, None), log_interval=15, no_pump=args.no_pump)
+    trainer.train_epoch(warm_loader, 0)
+    trainer.train_epoch(loader, 0)                          # also warms the timed loader's own pump/graphs
     _sync_all()
     e0.record()
     t0 = time.perf_counter()
-    e2e_epoch(K, W)
+    trainer.train_epoch(loader, 1)                          # K steps; returns after the last step finished
     e1.record()
     _sync_all()
     wall_ms = (time.perf_counter() - t0) * 1e3
     e2e_ms = _max_ranks(max(e0.elapsed_time(e1), wall_ms), dev)
     stepper.check_error()
-    loss_e2e = float(loss_ring[W + K - 1])
+    pumped = trainer._pump_for(loader) is not None
+    loss_e2e = float(trainer._loss_ring[K - 1]) if pumped else float(stepper.net.loss)
     div = stepper.replica_divergence()
 
     # ---- exposed communication per step: same device-timed loop with the cross-rank exchange elided ----
@@ -214,7 +210,8 @@ def run_own(args):
             "clocks": clocks,
             "e2e": {"value": imgs / (e2e_ms / 1e3), "unit": "images/s", "ms_per_step": e2e_ms / K,
                     "h2d_bytes_per_step": loader.h2d_bytes_per_batch, "d2h_bytes_per_step": 4,
-                    "input_format": args.input},
+                    "input_format": args.input,
+                    "api": "b200dp.engine.Trainer.train_epoch" + (" (native C++ step pump)" if pumped else " (Python loop)")},
             "gpu_launches": stepper.launches_per_step * K,
             "final_loss": {"device_path": loss_dev, "e2e_path": loss_e2e},
             "replica_divergence": div,

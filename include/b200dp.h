@@ -218,6 +218,38 @@ int b200dp_symm_import(const uint8_t handle[64], void** ptr_out);
 int b200dp_symm_close(void* imported_ptr);
 int b200dp_enable_peer_access(int peer_device);
 
+/* ---- native step pump (csrc/pump.cu) ---------------------------------------
+ * The host side of the hot loop in C++: replaces the DataLoader iteration, the two .cuda()
+ * copies and loss.item() of train.py:44-45,55.  For each step the pump gathers the step's samples
+ * (order[step*batch .. +batch) indexes the base arrays) into pinned ring slot step%depth, launches
+ * graph_exec[slot] — an instantiated CUDA graph whose first nodes copy host_x[slot]/host_y[slot]
+ * to the device and whose other nodes are the whole training step — and queues a 4-byte copy of
+ * *loss_dev into loss_host[step].  Only ring-slot reuse is synchronised (an event per slot), so the
+ * host runs up to depth-1 steps ahead of the GPU; a helper thread gathers ahead of the launcher.
+ * b200dp_pump_run returns once everything is queued; b200dp_pump_drain waits for the queued steps. */
+#define B200DP_PUMP_MAX_DEPTH 8
+typedef struct b200dp_pump b200dp_pump;
+typedef struct {
+    const void* images;        /* host base array, one sample = image_bytes contiguous bytes */
+    const int64_t* targets;    /* host base labels */
+    int64_t image_bytes;
+    int batch, depth;
+    void* host_x[B200DP_PUMP_MAX_DEPTH];      /* pinned ring: batch*image_bytes each */
+    void* host_y[B200DP_PUMP_MAX_DEPTH];      /* pinned ring: batch int64 each */
+    void* graph_exec[B200DP_PUMP_MAX_DEPTH];  /* cudaGraphExec_t per slot */
+    const float* loss_dev;     /* device scalar the step writes its batch-mean loss to */
+} b200dp_pump_desc;
+int b200dp_pump_create(b200dp_pump** out, const b200dp_pump_desc* desc);
+int b200dp_pump_run(b200dp_pump* p, const int64_t* order, int n_steps, float* loss_host /* pinned, nullable */,
+                    b200dp_stream_t s);
+int b200dp_pump_wait_first(b200dp_pump* p);   /* until step 0 of the latest run (and its loss copy) finished */
+int b200dp_pump_drain(b200dp_pump* p);
+int b200dp_pump_destroy(b200dp_pump* p);
+
+/* NVTX ranges for host-side phases (visible in Nsight tools; no-ops otherwise). */
+void b200dp_nvtx_push(const char* name);
+void b200dp_nvtx_pop(void);
+
 #ifdef __cplusplus
 }
 #endif
