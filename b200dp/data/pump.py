@@ -3,8 +3,9 @@
 The reference's hot loop (train.py:44-57) pays, per batch, a DataLoader ``__next__``, two synchronous
 ``.cuda()`` copies and the Python of the step itself.  Here one ctypes call queues a whole run of
 steps: a C++ loop gathers each step's shuffled samples of this rank's shard into a pinned ring slot,
-launches one CUDA graph (H2D copies of that slot + the entire training step) and queues the 4-byte
-loss read-back into a pinned array.  Python only sees chunks of steps (one chunk per log line).
+launches one CUDA graph per step — the entire training step, with the upload of the NEXT step's slot as
+a parallel branch — and every step's loss lands in a pinned array, stored there by the step's last
+kernel through mapped memory.  Python only sees chunks of steps (one chunk per log line).
 
 :class:`StepPump` owns the pinned/device rings and the per-slot graphs of one
 :class:`~b200dp.models.fused.NativeStepper`.
@@ -41,6 +42,9 @@ class StepPump:
         self._graphs = []
         self._handle: Optional[int] = None
         self._loss_keepalive = None
+        self._sink_host = torch.zeros(4, dtype=torch.int64)
+        self._sink_stage = [torch.zeros(4, dtype=torch.int64).pin_memory() for _ in range(8)]   # in-flight H2D sources
+        self._sink_i = 0
 
     # graphs are captured lazily: the stepper wants two eager steps first (lazy module loading)
     def _ensure_graphs(self) -> None:
@@ -49,12 +53,18 @@ class StepPump:
         st = self.stepper
         assert st._warm >= 2, "run two eager steps before capturing"
         torch.cuda.synchronize(st.device)
+        copy_stream = torch.cuda.Stream(device=st.device)
         for s in range(self.depth):
+            nxt = (s + 1) % self.depth
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, capture_error_mode="thread_local"):
-                self.dev_x[s].copy_(self.host_x[s], non_blocking=True)     # H2D memcpy nodes
-                self.dev_y[s].copy_(self.host_y[s], non_blocking=True)
-                st._step_body(self.dev_x[s], self.dev_y[s])
+                main = torch.cuda.current_stream(st.device)
+                copy_stream.wait_stream(main)
+                with torch.cuda.stream(copy_stream):              # branch 1: upload the NEXT step's batch
+                    self.dev_x[nxt].copy_(self.host_x[nxt], non_blocking=True)
+                    self.dev_y[nxt].copy_(self.host_y[nxt], non_blocking=True)
+                st._step_body(self.dev_x[s], self.dev_y[s])       # branch 2: this step
+                main.wait_stream(copy_stream)
             self._graphs.append(g)
         d = native.PumpDesc()
         d.images, d.targets = self.images.data_ptr(), self.targets.data_ptr()
@@ -62,8 +72,8 @@ class StepPump:
         d.batch, d.depth = self.batch, self.depth
         for s in range(self.depth):
             d.host_x[s], d.host_y[s] = self.host_x[s].data_ptr(), self.host_y[s].data_ptr()
+            d.dev_x[s], d.dev_y[s] = self.dev_x[s].data_ptr(), self.dev_y[s].data_ptr()
             d.graph_exec[s] = int(self._graphs[s].raw_cuda_graph_exec())
-        d.loss_dev = st.net.loss.data_ptr()
         self._handle = native.pump_create(d)
 
     def invalidate(self) -> None:
@@ -80,7 +90,8 @@ class StepPump:
         return loss
 
     def run(self, order: torch.Tensor, n_steps: int, loss_host: Optional[torch.Tensor] = None) -> None:
-        """Queue ``n_steps`` steps (returns before they finish).  ``loss_host``: pinned float32 [>= n_steps]."""
+        """Queue ``n_steps`` steps (returns before they finish).  ``loss_host``: pinned float32 [>= n_steps];
+        element k receives step k's loss, stored by the step's last kernel (mapped memory, no copy command)."""
         st = self.stepper
         k0 = 0
         while st._warm < 2 and k0 < n_steps:            # the stepper's first two steps run eagerly
@@ -93,9 +104,20 @@ class StepPump:
         self._ensure_graphs()
         st._sync_hyper()
         n = n_steps - k0
+        # tell the device where this run's losses go: {array, generation of its element 0, length}
+        if loss_host is not None:
+            assert loss_host.dtype == torch.float32 and not loss_host.is_cuda and loss_host.numel() >= n_steps
+            self._sink_host[0] = loss_host.data_ptr() + 4 * k0
+            self._sink_host[1] = st.optimizer.step_count + 1
+            self._sink_host[2] = n
+        else:
+            self._sink_host.zero_()
+        self._sink_stage[self._sink_i].copy_(self._sink_host)
+        st.loss_sink.copy_(self._sink_stage[self._sink_i], non_blocking=True)
+        self._sink_i = (self._sink_i + 1) % len(self._sink_stage)
         st.optimizer.step_count += n
         self._loss_keepalive = loss_host
-        native.pump_run(self._handle, order[k0 * self.batch:], n, None if loss_host is None else loss_host[k0:])
+        native.pump_run(self._handle, order[k0 * self.batch:], n)
 
     def wait_first(self) -> None:
         if self._handle is not None:
@@ -104,9 +126,11 @@ class StepPump:
     def drain(self) -> None:
         if self._handle is not None:
             native.pump_drain(self._handle)
+            torch.cuda.current_stream(self.stepper.device).synchronize()
 
     def close(self) -> None:
         if self._handle is not None:
             native.pump_destroy(self._handle)
             self._handle = None
+            self.stepper.loss_sink.zero_()
         self._graphs.clear()

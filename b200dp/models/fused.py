@@ -231,6 +231,8 @@ class NativeStepper:
         self.hyper_host = torch.zeros(8, dtype=torch.float32).pin_memory()
         self._hyper_cache: Optional[Tuple] = None
         self.step_counter = torch.zeros(4, dtype=torch.int32, device=self.device)
+        # {mapped pinned loss array, generation at its index 0, its length}: see b200dp_reduce_update
+        self.loss_sink = torch.zeros(4, dtype=torch.int64, device=self.device)
         self._graphs: Dict[Tuple[int, int, int], torch.cuda.CUDAGraph] = {}
         self._static_x: Optional[torch.Tensor] = None
         self._static_y: Optional[torch.Tensor] = None
@@ -261,7 +263,8 @@ class NativeStepper:
                              net.partials if is_conv else None, net.cur_partials if is_conv else 0,
                              net.partial_stride if is_conv else 0, opt.hyper.code(), self.hyper_dev,
                              self.step_counter, bucket_index == 2,
-                             self.comm.struct_for(b.numel * 4) if (self.comm and not self._comm_off) else None)
+                             self.comm.struct_for(b.numel * 4) if (self.comm and not self._comm_off) else None,
+                             net.loss, self.loss_sink)
 
     def _step_body(self, x: torch.Tensor, y: torch.Tensor) -> None:
         main = torch.cuda.current_stream(self.device)

@@ -47,8 +47,8 @@ class Comm(C.Structure):
 class PumpDesc(C.Structure):
     _fields_ = [("images", C.c_void_p), ("targets", C.c_void_p), ("image_bytes", C.c_int64),
                 ("batch", C.c_int), ("depth", C.c_int),
-                ("host_x", C.c_void_p * 8), ("host_y", C.c_void_p * 8), ("graph_exec", C.c_void_p * 8),
-                ("loss_dev", C.c_void_p)]
+                ("host_x", C.c_void_p * 8), ("host_y", C.c_void_p * 8), ("dev_x", C.c_void_p * 8),
+                ("dev_y", C.c_void_p * 8), ("graph_exec", C.c_void_p * 8)]
 
 
 def lib_path() -> str:
@@ -85,7 +85,7 @@ def load(build_if_missing: bool = True):
     lib.b200dp_tc_conv_wgrad.argtypes = [i, vp, i, f, f, vp, vp, i, vp, vp, i, i, i, Dims, vp]
     lib.b200dp_conv_bwd_num_partials.argtypes = [Dims]
     lib.b200dp_conv_bwd.argtypes = [vp, i, f, f, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, Dims, vp]
-    lib.b200dp_reduce_update.argtypes = [vp, vp, vp, vp, vp, i, i, vp, i, i, i, vp, vp, i, C.POINTER(Comm), vp]
+    lib.b200dp_reduce_update.argtypes = [vp, vp, vp, vp, vp, i, i, vp, i, i, i, vp, vp, i, C.POINTER(Comm), vp, vp, vp]
     lib.b200dp_symm_alloc.argtypes = [C.POINTER(vp), C.c_uint64]
     lib.b200dp_symm_free.argtypes = [vp]
     lib.b200dp_symm_export.argtypes = [vp, C.c_char_p]
@@ -93,7 +93,7 @@ def load(build_if_missing: bool = True):
     lib.b200dp_symm_close.argtypes = [vp]
     lib.b200dp_enable_peer_access.argtypes = [i]
     lib.b200dp_pump_create.argtypes = [C.POINTER(vp), C.POINTER(PumpDesc)]
-    lib.b200dp_pump_run.argtypes = [vp, vp, i, vp, vp]
+    lib.b200dp_pump_run.argtypes = [vp, vp, i, vp]
     lib.b200dp_pump_wait_first.argtypes = [vp]
     lib.b200dp_pump_drain.argtypes = [vp]
     lib.b200dp_pump_destroy.argtypes = [vp]
@@ -220,11 +220,12 @@ def conv_bwd(x, mean, std, p1, idx1, p2, idx2, dp2, w2, partials, stride, off_w1
 # ---- reduce + update -----------------------------------------------------------
 def reduce_update(param, grad, state0, state1, shadow, start: int, count: int, partials, n_partials: int,
                   partial_stride: int, opt_kind: int, hyper, step_counter, last_bucket: bool,
-                  comm: Optional[Comm]) -> None:
+                  comm: Optional[Comm], loss_src=None, loss_sink=None) -> None:
     check(load().b200dp_reduce_update(_p(param), _p(grad), _p(state0), _p(state1), _p(shadow), start, count,
                                       _p(partials), n_partials, partial_stride, opt_kind, _p(hyper),
                                       _p(step_counter), int(last_bucket),
-                                      C.byref(comm) if comm is not None else None, _stream()), "reduce_update")
+                                      C.byref(comm) if comm is not None else None, _p(loss_src), _p(loss_sink),
+                                      _stream()), "reduce_update")
 
 
 # ---- symmetric memory ------------------------------------------------------------
@@ -261,11 +262,11 @@ def pump_create(desc: PumpDesc) -> int:
     return h.value
 
 
-def pump_run(handle: int, order: torch.Tensor, n_steps: int, loss_host: Optional[torch.Tensor]) -> None:
-    """``order``: contiguous CPU int64 sample indices (n_steps*batch of them are read);
-    ``loss_host``: pinned float32 tensor with >= n_steps elements, or None."""
+def pump_run(handle: int, order: torch.Tensor, n_steps: int) -> None:
+    """``order``: contiguous CPU int64 sample indices (n_steps*batch of them are read)."""
     assert order.dtype == torch.int64 and order.is_contiguous() and not order.is_cuda
-    check(load().b200dp_pump_run(handle, order.data_ptr(), n_steps, _p(loss_host), _stream()), "pump_run")
+    assert order.numel() >= n_steps
+    check(load().b200dp_pump_run(handle, order.data_ptr(), n_steps, _stream()), "pump_run")
 
 
 def pump_wait_first(handle: int) -> None:

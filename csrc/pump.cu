@@ -1,15 +1,15 @@
 // Native step pump: the per-batch host work of an epoch, done by a C++ loop instead of Python.
 //
 // Replaces the reference's hot loop plumbing (train.py:44-45 DataLoader iteration + .cuda() copies,
-// train.py:55 loss.item()):  for every step the pump gathers the step's (shuffled) samples of this
-// rank's shard into a pinned ring slot, launches ONE instantiated CUDA graph whose first nodes copy
-// that slot to the device and whose remaining nodes are the whole training step (forward, backward,
-// fused reduce+update), and queues a 4-byte device->host copy of the step's loss into a pinned array.
-// Nothing is synchronised except ring-slot reuse: before slot s is refilled the pump waits for the
-// event recorded after the last graph that read it, so the host runs at most `depth-1` steps ahead.
-//
-// A helper thread pre-gathers the next slot while the calling thread launches, so the per-step host
-// cost on the launching thread is a graph launch + one tiny copy + one event record.
+// train.py:55 loss.item()).  Step k of a run uses ring slot k%depth.  Its CUDA graph has two branches:
+// the whole training step (forward, backward, fused reduce+update) on device slot k%depth, and, beside
+// it, the host->device copies of pinned slot (k+1)%depth — the NEXT step's batch — so the upload never
+// sits on the step's critical path.  The step's loss reaches the host without a copy command: the
+// last reduce+update kernel of the step stores it into a mapped pinned array (see b200dp_reduce_update).
+// The only host<->GPU synchronisation is ring-slot reuse: a helper thread gathers step j's (shuffled)
+// samples into pinned slot j%depth as soon as the graph that last read the slot has finished, while
+// the calling thread launches; the host therefore runs up to depth-1 steps ahead of the GPU and the
+// launching thread's per-step cost is one cudaGraphLaunch and one event record.
 #include <nvtx3/nvToolsExt.h>
 #include <string.h>
 
@@ -24,18 +24,19 @@ namespace b200dp {
 
 struct Pump {
     b200dp_pump_desc d;
-    cudaEvent_t done[B200DP_PUMP_MAX_DEPTH];
+    // slot_ev[s]: recorded after the last queued operation that READS pinned slot s (the graph whose prefetch
+    // branch copies it to the device, or the explicit copy of a run's first step)
+    cudaEvent_t slot_ev[B200DP_PUMP_MAX_DEPTH];
+    bool slot_pending[B200DP_PUMP_MAX_DEPTH];
     cudaEvent_t first_done;                  // recorded after step 0 of the latest run(): lets the caller log its loss
     bool first_valid = false;
-    bool pending[B200DP_PUMP_MAX_DEPTH];
-    // helper-thread hand-off: the launcher posts "gather step k into slot s", the helper answers "filled"
+    // launcher <-> helper hand-off
     std::thread helper;
     std::mutex mu;
     std::condition_variable cv;
     const int64_t* order = nullptr;
-    long req = 0, filled = 0, total = 0;     // steps requested / gathered so far in the current run()
-    bool quit = false, busy = false;
-    bool slot_free[B200DP_PUMP_MAX_DEPTH];
+    long req = 0, filled = 0, launched = 0;  // steps to gather / gathered / graphs launched in the current run()
+    bool quit = false, busy = false, failed = false;
     int device = 0;
 
     void gather(long step) {
@@ -51,18 +52,34 @@ struct Pump {
         }
     }
 
+    // Pinned slot j%depth was last read on behalf of step j-depth: by graph j-depth-1 (its prefetch branch),
+    // whose event exists once `launched >= j-depth`, or, for the run's first step, by the explicit copy
+    // queued before graph 0.  Readers queued by earlier runs still have slot_pending set.
     void helper_main() {
         cudaSetDevice(device);
         std::unique_lock<std::mutex> lk(mu);
         for (;;) {
-            cv.wait(lk, [&] { return quit || (filled < req && slot_free[filled % d.depth]); });
+            cv.wait(lk, [&] {
+                if (quit) return true;
+                if (filled >= req) return false;
+                const long j = filled;                         // reader of slot j%depth before us: see above
+                return j < d.depth || (j == d.depth ? launched >= 1 : launched >= j - d.depth);
+            });
             if (quit) return;
             const long k = filled;
-            slot_free[k % d.depth] = false;
+            const int s = (int)(k % d.depth);
             busy = true;
+            const bool wait_ev = slot_pending[s];
             lk.unlock();
+            if (wait_ev && cudaEventSynchronize(slot_ev[s]) != cudaSuccess) {
+                lk.lock();
+                failed = true; busy = false; filled = req;
+                cv.notify_all();
+                continue;
+            }
             gather(k);
             lk.lock();
+            slot_pending[s] = false;
             busy = false;
             filled = k + 1;
             cv.notify_all();
@@ -79,14 +96,14 @@ extern "C" int b200dp_pump_create(b200dp_pump** out, const b200dp_pump_desc* des
     B200DP_REQUIRE(desc->depth >= 2 && desc->depth <= B200DP_PUMP_MAX_DEPTH, "depth 2..8");
     B200DP_REQUIRE(desc->batch > 0 && desc->image_bytes > 0 && desc->images && desc->targets, "bad dataset");
     for (int s = 0; s < desc->depth; ++s)
-        B200DP_REQUIRE(desc->host_x[s] && desc->host_y[s] && desc->graph_exec[s], "ring slot incomplete");
+        B200DP_REQUIRE(desc->host_x[s] && desc->host_y[s] && desc->dev_x[s] && desc->dev_y[s] && desc->graph_exec[s],
+                       "ring slot incomplete");
     Pump* p = new Pump();
     p->d = *desc;
     B200DP_CHECK(cudaGetDevice(&p->device));
     for (int s = 0; s < desc->depth; ++s) {
-        B200DP_CHECK(cudaEventCreateWithFlags(&p->done[s], cudaEventDisableTiming));
-        p->pending[s] = false;
-        p->slot_free[s] = true;
+        B200DP_CHECK(cudaEventCreateWithFlags(&p->slot_ev[s], cudaEventDisableTiming));
+        p->slot_pending[s] = false;
     }
     B200DP_CHECK(cudaEventCreateWithFlags(&p->first_done, cudaEventDisableTiming));
     p->helper = std::thread([p] { p->helper_main(); });
@@ -94,42 +111,58 @@ extern "C" int b200dp_pump_create(b200dp_pump** out, const b200dp_pump_desc* des
     return 0;
 }
 
-extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_steps, float* loss_host,
-                               b200dp_stream_t stream) {
+extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_steps, b200dp_stream_t stream) {
     Pump* p = (Pump*)handle;
     B200DP_REQUIRE(p && order && n_steps >= 0, "bad arguments");
+    if (n_steps == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
+    const int depth = p->d.depth;
     nvtxRangePushA("b200dp.pump_run");
     {
         std::lock_guard<std::mutex> lk(p->mu);
         p->order = order;
         p->req = n_steps;
         p->filled = 0;
-        for (int s = 0; s < p->d.depth; ++s) p->slot_free[s] = !p->pending[s];
+        p->launched = 0;
+        p->failed = false;
     }
     p->cv.notify_all();
+    auto wait_filled = [&](long k) {
+        std::unique_lock<std::mutex> lk(p->mu);
+        p->cv.wait(lk, [&] { return p->filled > k; });
+        return !p->failed;
+    };
+    auto mark = [&](int s) -> cudaError_t {      // the operation just queued reads pinned slot s
+        cudaError_t e = cudaEventRecord(p->slot_ev[s], st);
+        std::lock_guard<std::mutex> lk(p->mu);
+        p->slot_pending[s] = true;
+        return e;
+    };
     int rc = 0;
-    for (long k = 0; k < n_steps; ++k) {
-        const int s = (int)(k % p->d.depth);
-        if (p->pending[s]) {                                   // the graph that last read this slot must be done
-            cudaError_t e = cudaEventSynchronize(p->done[s]);
-            if (e != cudaSuccess) { set_last_error("pump: event sync: %s", cudaGetErrorString(e)); rc = (int)e; break; }
-            p->pending[s] = false;
-            std::lock_guard<std::mutex> lk(p->mu);
-            p->slot_free[s] = true;
-            p->cv.notify_all();
+    cudaError_t e = cudaSuccess;
+    // the first step's batch goes up with two explicit copies; every later batch is prefetched by the
+    // graph of the step before it
+    if (!wait_filled(0)) { set_last_error("pump: waiting for a ring slot failed"); rc = (int)cudaErrorUnknown; }
+    if (rc == 0) {
+        e = cudaMemcpyAsync(p->d.dev_x[0], p->d.host_x[0], (size_t)p->d.batch * p->d.image_bytes, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(p->d.dev_y[0], p->d.host_y[0], (size_t)p->d.batch * sizeof(int64_t), cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = mark(0);
+        if (e != cudaSuccess) { set_last_error("pump: first copy: %s", cudaGetErrorString(e)); rc = (int)e; }
+    }
+    for (long k = 0; rc == 0 && k < n_steps; ++k) {
+        if (k + 1 < n_steps && !wait_filled(k + 1)) {          // graph k's prefetch branch reads pinned slot (k+1)%depth
+            set_last_error("pump: waiting for a ring slot failed"); rc = (int)cudaErrorUnknown; break;
         }
-        {
-            std::unique_lock<std::mutex> lk(p->mu);
-            p->cv.wait(lk, [&] { return p->filled > k; });     // helper has gathered step k
-        }
-        cudaError_t e = cudaGraphLaunch((cudaGraphExec_t)p->d.graph_exec[s], st);
-        if (e == cudaSuccess && loss_host)
-            e = cudaMemcpyAsync(loss_host + k, p->d.loss_dev, sizeof(float), cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess) e = cudaEventRecord(p->done[s], st);
+        e = cudaGraphLaunch((cudaGraphExec_t)p->d.graph_exec[k % depth], st);
+        if (e == cudaSuccess) e = mark((int)((k + 1) % depth));
         if (e == cudaSuccess && k == 0) { e = cudaEventRecord(p->first_done, st); p->first_valid = true; }
         if (e != cudaSuccess) { set_last_error("pump: step %ld: %s", k, cudaGetErrorString(e)); rc = (int)e; break; }
-        p->pending[s] = true;
+        {
+            std::lock_guard<std::mutex> lk(p->mu);
+            p->launched = k + 1;
+        }
+        p->cv.notify_all();
     }
     {   // stop the helper from touching `order` after we return
         std::unique_lock<std::mutex> lk(p->mu);
@@ -143,11 +176,15 @@ extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_
 extern "C" int b200dp_pump_drain(b200dp_pump* handle) {
     Pump* p = (Pump*)handle;
     B200DP_REQUIRE(p, "null pump");
-    for (int s = 0; s < p->d.depth; ++s)
-        if (p->pending[s]) {
-            B200DP_CHECK(cudaEventSynchronize(p->done[s]));
-            p->pending[s] = false;
+    for (int s = 0; s < p->d.depth; ++s) {
+        bool pend;
+        { std::lock_guard<std::mutex> lk(p->mu); pend = p->slot_pending[s]; }
+        if (pend) {
+            B200DP_CHECK(cudaEventSynchronize(p->slot_ev[s]));
+            std::lock_guard<std::mutex> lk(p->mu);
+            p->slot_pending[s] = false;
         }
+    }
     return 0;
 }
 
@@ -168,8 +205,8 @@ extern "C" int b200dp_pump_destroy(b200dp_pump* handle) {
     p->cv.notify_all();
     if (p->helper.joinable()) p->helper.join();
     for (int s = 0; s < p->d.depth; ++s) {
-        if (p->pending[s]) cudaEventSynchronize(p->done[s]);
-        cudaEventDestroy(p->done[s]);
+        if (p->slot_pending[s]) cudaEventSynchronize(p->slot_ev[s]);
+        cudaEventDestroy(p->slot_ev[s]);
     }
     cudaEventDestroy(p->first_done);
     delete p;

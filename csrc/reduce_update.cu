@@ -40,6 +40,7 @@ struct RUArgs {
     const float* hyper;
     uint32_t* step_counter;   // [0] generation, [1] ticket, [2] error flag
     int last_bucket;
+    const float* loss_src; const unsigned long long* loss_sink;
     b200dp_comm comm;
     int slice;
 };
@@ -337,6 +338,15 @@ __global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
         if (tid == 0) {
             __threadfence();
             if (atomicAdd(a.step_counter + 1, 1u) == gridDim.x - 1) {
+                if (a.loss_sink != nullptr) {
+                    // deliver the step's loss to the host: a 4-byte store into a mapped pinned array
+                    // (no copy command, nothing for the next step to wait on)
+                    const unsigned long long ring = a.loss_sink[0], idx = (unsigned long long)gen - a.loss_sink[1];
+                    if (ring != 0ull && idx < a.loss_sink[2]) {
+                        reinterpret_cast<volatile float*>(ring)[idx] = __ldcg(a.loss_src);
+                        __threadfence_system();
+                    }
+                }
                 a.step_counter[1] = 0u;
                 __threadfence();
                 a.step_counter[0] = gen;
@@ -353,7 +363,7 @@ extern "C" int b200dp_reduce_update(float* param, float* grad, float* state0, fl
                                     uint16_t* shadow_bf16, int start, int count, const float* partials,
                                     int n_partials, int partial_stride, int opt_kind, const float* hyper,
                                     uint32_t* step_counter, int last_bucket, const b200dp_comm* comm,
-                                    b200dp_stream_t s) {
+                                    const float* loss_src, const uint64_t* loss_sink, b200dp_stream_t s) {
     B200DP_REQUIRE(start % 128 == 0 && count % 4 == 0 && count > 0, "bucket must be 128-aligned");
     B200DP_REQUIRE(opt_kind >= 0 && opt_kind <= 2, "opt_kind 0 adadelta, 1 sgd, 2 adam");
     RUArgs a{};
@@ -361,6 +371,7 @@ extern "C" int b200dp_reduce_update(float* param, float* grad, float* state0, fl
     a.start = start; a.count = count;
     a.partials = partials; a.n_partials = n_partials; a.partial_stride = partial_stride;
     a.opt_kind = opt_kind; a.hyper = hyper; a.step_counter = step_counter; a.last_bucket = last_bucket;
+    a.loss_src = loss_src; a.loss_sink = (loss_src && last_bucket) ? (const unsigned long long*)loss_sink : nullptr;
     if (comm) {
         a.comm = *comm;
         B200DP_REQUIRE(comm->world >= 1 && comm->world <= 8, "world size 1..8");

@@ -186,7 +186,11 @@ int b200dp_conv_bwd_noalloc(const void* x, int in_is_u8, float mean, float std, 
  * scheduler changes.
  * step_counter (device, uint32[4], zero-initialised): [0] generation (= optimizer steps done),
  * [1] ticket, [2] error flag (1 = a peer did not answer within the spin bound).  The LAST
- * bucket launch of a step (last_bucket != 0) advances the generation. */
+ * bucket launch of a step (last_bucket != 0) advances the generation.
+ * loss_src / loss_sink (both nullable; used by the last bucket launch only): loss_sink is a device
+ * uint64[3] = {address of a mapped pinned float array (0 = off), generation stored at index 0,
+ * array length}; the step with generation g stores *loss_src into array[g - sink[1]] — how the
+ * loss reaches the host without a copy command (train.py:55 loss.item()). */
 typedef struct {
     int world, rank;
     int algo;                 /* 0 one-shot: every rank reads every peer's slice (latency regime);
@@ -206,7 +210,8 @@ typedef struct {
 int b200dp_reduce_update(float* param, float* grad, float* state0, float* state1, uint16_t* shadow_bf16,
                          int start, int count, const float* partials, int n_partials, int partial_stride,
                          int opt_kind, const float* hyper, uint32_t* step_counter, int last_bucket,
-                         const b200dp_comm* comm, b200dp_stream_t s);
+                         const b200dp_comm* comm, const float* loss_src, const uint64_t* loss_sink,
+                         b200dp_stream_t s);
 
 /* ---- symmetric memory plumbing (replaces the NCCL communicator of train.py:26-31) ----
  * Allocation of peer-mappable device memory and exchange via CUDA IPC handles
@@ -220,12 +225,15 @@ int b200dp_enable_peer_access(int peer_device);
 
 /* ---- native step pump (csrc/pump.cu) ---------------------------------------
  * The host side of the hot loop in C++: replaces the DataLoader iteration, the two .cuda()
- * copies and loss.item() of train.py:44-45,55.  For each step the pump gathers the step's samples
- * (order[step*batch .. +batch) indexes the base arrays) into pinned ring slot step%depth, launches
- * graph_exec[slot] — an instantiated CUDA graph whose first nodes copy host_x[slot]/host_y[slot]
- * to the device and whose other nodes are the whole training step — and queues a 4-byte copy of
- * *loss_dev into loss_host[step].  Only ring-slot reuse is synchronised (an event per slot), so the
- * host runs up to depth-1 steps ahead of the GPU; a helper thread gathers ahead of the launcher.
+ * copies and loss.item() of train.py:44-45,55.  Step k of a run uses ring slot k%depth:
+ * graph_exec[k%depth] is an instantiated CUDA graph with two parallel branches — the whole
+ * training step reading dev_x/dev_y[k%depth], and the host->device copies of pinned slot
+ * (k+1)%depth into device slot (k+1)%depth (the next step's batch, uploaded off the critical
+ * path).  The pump gathers the samples (order[k*batch .. +batch) indexes the base arrays) into
+ * the pinned slots from a helper thread, uploads the first batch of a run itself, and launches
+ * the graphs.  Only ring-slot reuse is synchronised (one event per pinned slot), so the host
+ * runs up to depth-1 steps ahead of the GPU.  The loss of every step is delivered by the step's
+ * last b200dp_reduce_update launch (its loss_sink argument).
  * b200dp_pump_run returns once everything is queued; b200dp_pump_drain waits for the queued steps. */
 #define B200DP_PUMP_MAX_DEPTH 8
 typedef struct b200dp_pump b200dp_pump;
@@ -236,13 +244,13 @@ typedef struct {
     int batch, depth;
     void* host_x[B200DP_PUMP_MAX_DEPTH];      /* pinned ring: batch*image_bytes each */
     void* host_y[B200DP_PUMP_MAX_DEPTH];      /* pinned ring: batch int64 each */
+    void* dev_x[B200DP_PUMP_MAX_DEPTH];       /* device ring, same sizes */
+    void* dev_y[B200DP_PUMP_MAX_DEPTH];
     void* graph_exec[B200DP_PUMP_MAX_DEPTH];  /* cudaGraphExec_t per slot */
-    const float* loss_dev;     /* device scalar the step writes its batch-mean loss to */
 } b200dp_pump_desc;
 int b200dp_pump_create(b200dp_pump** out, const b200dp_pump_desc* desc);
-int b200dp_pump_run(b200dp_pump* p, const int64_t* order, int n_steps, float* loss_host /* pinned, nullable */,
-                    b200dp_stream_t s);
-int b200dp_pump_wait_first(b200dp_pump* p);   /* until step 0 of the latest run (and its loss copy) finished */
+int b200dp_pump_run(b200dp_pump* p, const int64_t* order, int n_steps, b200dp_stream_t s);
+int b200dp_pump_wait_first(b200dp_pump* p);   /* until step 0 of the latest run finished */
 int b200dp_pump_drain(b200dp_pump* p);
 int b200dp_pump_destroy(b200dp_pump* p);
 
