@@ -1,0 +1,9 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 300 python -m pytest tests/test_tc_win_gpu.py -m gpu -q --tb=short -p no:cacheprovider -x > gpurun_out/pytest_tcw.log 2>&1
+echo "pytest rc=$?" >> gpurun_out/pytest_tcw.log
+tail -n 6 gpurun_out/pytest_tcw.log | cut -c1-300
+timeout 300 python bench/tcw_probe.py > gpurun_out/tcw_probe.log 2>&1 && \
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:win_conv --launch-skip 6 -c 48 -f -o gpurun_out/tcw_full python bench/tcw_probe.py > gpurun_out/ncu_tcw.log 2>&1
+tail -n 8 gpurun_out/tcw_probe.log | cut -c1-400
+tail -n 3 gpurun_out/ncu_tcw.log | cut -c1-300

@@ -128,6 +128,23 @@ int b200dp_tc_conv_wgrad(int layer, const void* x, int in_is_u8, float mean, flo
                          const float* act, int ld_act, const uint8_t* idx, float* partials,
                          int partial_stride, int off_w, int off_b, b200dp_dims d, b200dp_stream_t s);
 
+/* "Window-tile" convolutions (csrc/tc_win.cu): tcgen05 implicit GEMM that reads the staged image in place —
+ * an accumulator tile is a 16x8-pixel window addressed by a no-swizzle K-major descriptor, a filter tap is a
+ * start-address shift, so no im2col operand is ever written.  Same tensors and semantics as the
+ * b200dp_tc_conv* entry points, except that the weights come pre-packed: call b200dp_tcw_pack_weights once
+ * per step (after the optimizer update) into a scratch of b200dp_tcw_pack_floats(d) floats; it packs the
+ * first layer's forward panels, the second layer's forward panels and its flipped data-gradient panels.
+ * Supported geometries: (in_ch,c1,c2) = (1,6,16) and (3,24,64).
+ * Replaces cnn.py:10-15 and their backward (train.py:49); cuDNN in the reference. */
+long b200dp_tcw_pack_floats(b200dp_dims d);
+int b200dp_tcw_pack_weights(const float* w1, const float* w2, float* wpack, b200dp_dims d, b200dp_stream_t s);
+int b200dp_tcw_conv1_fwd(const void* x, int in_is_u8, float mean, float std, const float* wpack, const float* b,
+                         float* p1, uint8_t* idx1, b200dp_dims d, b200dp_stream_t s);
+int b200dp_tcw_conv2_fwd(const float* p1, const float* wpack, const float* b, float* p2, uint8_t* idx2,
+                         b200dp_dims d, b200dp_stream_t s);
+int b200dp_tcw_conv2_dgrad(const float* dp2, const float* p2, const uint8_t* idx2, const float* wpack,
+                           const float* p1, float* g1, b200dp_dims d, b200dp_stream_t s);
+
 /* Fused convolution backward for one step: pool2-bwd + leaky-bwd + conv2 dgrad
  * + conv2 wgrad/bgrad + pool1-bwd + leaky-bwd + conv1 wgrad/bgrad (no conv1
  * dgrad: the input needs no gradient).   train.py:49 / cnn.py:9-15.
