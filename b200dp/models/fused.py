@@ -50,7 +50,7 @@ class NativeLeNet:
         native.load()
         self.cfg, self.B, self.device, self.spec = cfg, int(batch), torch.device(device), spec
         self.tc = bool(tc)
-        # convolutions: tcgen05 implicit GEMM (csrc/tc_conv.cu) or CUDA cores (conv_fwd.cu / conv_bwd.cu).
+        # convolutions: window-tile tcgen05 kernels (csrc/tc_win.cu, tc_wgrad.cu) or CUDA cores (conv_fwd.cu / conv_bwd.cu).
         # The fused CUDA-core backward only exists for the reference geometry; the wide model needs tc.
         self.conv_tc = (cfg.width_mult > 1) if conv_tc is None else bool(conv_tc)
         if cfg.width_mult > 1 and not self.conv_tc:
@@ -96,7 +96,9 @@ class NativeLeNet:
         self.ticket = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.eval_acc = torch.zeros(2, dtype=torch.float64, device=self.device)
         self.g1 = torch.empty(B, c.c1, 14, 14, **f32) if self.conv_tc else None
-        self._num_partials = native.tc_conv_wgrad_num_partials if self.conv_tc else native.conv_bwd_num_partials
+        self._num_partials = native.tcw_conv_wgrad_num_partials if self.conv_tc else native.conv_bwd_num_partials
+        # per-tap weight panels of the tensor-core convolutions, re-packed at the start of every forward
+        self.wpack = torch.empty(native.tcw_pack_floats(self.dims(B)), **f32) if self.conv_tc else None
         self.n_partials = self._num_partials(self.dims(B))   # rows allocated (full batch)
         self.cur_partials = self.n_partials    # rows the last backward actually wrote (fewer on a ragged batch)
         self.partial_stride = self.bucket_conv.numel
@@ -117,10 +119,15 @@ class NativeLeNet:
         b = x.shape[0]
         assert b <= self.B and x.is_contiguous() and y.dtype == torch.int64
         d, w = self.dims(b), self.w
-        conv1, conv2 = (native.tc_conv1_fwd, native.tc_conv2_fwd) if self.conv_tc else (native.conv1_fwd, native.conv2_fwd)
-        conv1(x, w["ConvNet.1.weight"], w["ConvNet.1.bias"], self.p1, self.idx1 if train else None,
-              d, self.spec.mean, self.spec.std)
-        conv2(self.p1, w["ConvNet.4.weight"], w["ConvNet.4.bias"], self.p2, self.idx2 if train else None, d)
+        if self.conv_tc:
+            native.tcw_pack_weights(w["ConvNet.1.weight"], w["ConvNet.4.weight"], self.wpack, d)
+            native.tcw_conv1_fwd(x, self.wpack, w["ConvNet.1.bias"], self.p1, self.idx1 if train else None,
+                                 d, self.spec.mean, self.spec.std)
+            native.tcw_conv2_fwd(self.p1, self.wpack, w["ConvNet.4.bias"], self.p2, self.idx2 if train else None, d)
+        else:
+            native.conv1_fwd(x, w["ConvNet.1.weight"], w["ConvNet.1.bias"], self.p1, self.idx1 if train else None,
+                             d, self.spec.mean, self.spec.std)
+            native.conv2_fwd(self.p1, w["ConvNet.4.weight"], w["ConvNet.4.bias"], self.p2, self.idx2 if train else None, d)
         c = self.cfg
         k3 = c.c2 * 25
         if self.tc:
@@ -185,11 +192,11 @@ class NativeLeNet:
         self.cur_partials = self._num_partials(d)
         if self.conv_tc:
             ld_p2 = self.ld_p2 or k3
-            native.tc_conv2_dgrad(self.dp2, self.p2, self.idx2, w["ConvNet.4.weight"], self.p1, self.g1, d)
-            native.tc_conv_wgrad(2, self.p1, 0.0, 1.0, self.dp2, self.p2, ld_p2, self.idx2, self.partials,
-                                 self.partial_stride, ow2, ob2, d)
-            native.tc_conv_wgrad(1, x, self.spec.mean, self.spec.std, self.g1, None, 0, self.idx1, self.partials,
-                                 self.partial_stride, ow1, ob1, d)
+            native.tcw_conv2_dgrad(self.dp2, self.p2, self.idx2, self.wpack, self.p1, self.g1, d)
+            native.tcw_conv_wgrad(2, self.p1, 0.0, 1.0, self.dp2, self.p2, ld_p2, self.idx2, self.partials,
+                                  self.partial_stride, ow2, ob2, d)
+            native.tcw_conv_wgrad(1, x, self.spec.mean, self.spec.std, self.g1, None, 0, self.idx1, self.partials,
+                                  self.partial_stride, ow1, ob1, d)
         else:
             native.conv_bwd(x, self.spec.mean, self.spec.std, self.p1, self.idx1, self.p2, self.idx2, self.dp2,
                             w["ConvNet.4.weight"], self.partials, self.partial_stride, ow1, ob1, ow2, ob2, d)
@@ -239,7 +246,7 @@ class NativeStepper:
         self._warm = 0
         self._comm_off = False        # measurement aid: see set_comm_enabled
         self._pumps = []
-        self.launches_per_step = 13 if self.net.conv_tc else 11   # 5 fwd + 3 (5 with tc convs) bwd + 3 reduce/update
+        self.launches_per_step = 14 if self.net.conv_tc else 11   # (1 weight pack +) 5 fwd + 3 (5 with tc convs) bwd + 3 reduce/update
 
     # ---- optimizer scalars live on the device so graph replays see scheduler changes ----
     def _sync_hyper(self) -> None:

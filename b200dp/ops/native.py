@@ -78,11 +78,6 @@ def load(build_if_missing: bool = True):
     lib.b200dp_head_tail.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, vp]
     lib.b200dp_linear_bwd_group.argtypes = [C.POINTER(BwdProblem), i, vp]
     lib.b200dp_tc_gemm_group.argtypes = [C.POINTER(TcProblem), i, vp]
-    lib.b200dp_tc_conv1_fwd.argtypes = [vp, i, f, f, vp, vp, vp, vp, Dims, vp]
-    lib.b200dp_tc_conv2_fwd.argtypes = [vp, vp, vp, vp, vp, Dims, vp]
-    lib.b200dp_tc_conv2_dgrad.argtypes = [vp, vp, vp, vp, vp, vp, Dims, vp]
-    lib.b200dp_tc_conv_wgrad_num_partials.argtypes = [Dims]
-    lib.b200dp_tc_conv_wgrad.argtypes = [i, vp, i, f, f, vp, vp, i, vp, vp, i, i, i, Dims, vp]
     lib.b200dp_conv_bwd_num_partials.argtypes = [Dims]
     lib.b200dp_tcw_pack_floats.argtypes = [Dims]
     lib.b200dp_tcw_pack_floats.restype = C.c_long
@@ -90,6 +85,10 @@ def load(build_if_missing: bool = True):
     lib.b200dp_tcw_conv1_fwd.argtypes = [vp, i, f, f, vp, vp, vp, vp, Dims, vp]
     lib.b200dp_tcw_conv2_fwd.argtypes = [vp, vp, vp, vp, vp, Dims, vp]
     lib.b200dp_tcw_conv2_dgrad.argtypes = [vp, vp, vp, vp, vp, vp, Dims, vp]
+    lib.b200dp_tcw_set_debug.argtypes = [vp]
+    lib.b200dp_tcw_conv_wgrad_num_partials.argtypes = [Dims]
+    lib.b200dp_tcw_conv_wgrad.argtypes = [i, vp, i, f, f, vp, vp, i, vp, vp, i, i, i, Dims, vp]
+    lib.b200dp_tcw_set_debug.restype = None
     lib.b200dp_conv_bwd.argtypes = [vp, i, f, f, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, Dims, vp]
     lib.b200dp_reduce_update.argtypes = [vp, vp, vp, vp, vp, i, i, vp, i, i, i, vp, vp, i, C.POINTER(Comm), vp, vp, vp]
     lib.b200dp_symm_alloc.argtypes = [C.POINTER(vp), C.c_uint64]
@@ -150,30 +149,6 @@ def conv2_fwd(p1, w, b, p2, idx2, dims: Dims) -> None:
     check(load().b200dp_conv2_fwd(_p(p1), _p(w), _p(b), _p(p2), _p(idx2), dims, _stream()), "conv2_fwd")
 
 
-def tc_conv1_fwd(x, w, b, p1, idx1, dims: Dims, mean: float, std: float) -> None:
-    check(load().b200dp_tc_conv1_fwd(_p(x), int(x.dtype == torch.uint8), mean, std, _p(w), _p(b), _p(p1), _p(idx1),
-                                     dims, _stream()), "tc_conv1_fwd")
-
-
-def tc_conv2_fwd(p1, w, b, p2, idx2, dims: Dims) -> None:
-    check(load().b200dp_tc_conv2_fwd(_p(p1), _p(w), _p(b), _p(p2), _p(idx2), dims, _stream()), "tc_conv2_fwd")
-
-
-def tc_conv2_dgrad(dp2, p2, idx2, w2, p1, g1, dims: Dims) -> None:
-    check(load().b200dp_tc_conv2_dgrad(_p(dp2), _p(p2), _p(idx2), _p(w2), _p(p1), _p(g1), dims, _stream()),
-          "tc_conv2_dgrad")
-
-
-def tc_conv_wgrad_num_partials(dims: Dims) -> int:
-    return int(load().b200dp_tc_conv_wgrad_num_partials(dims))
-
-
-def tc_conv_wgrad(layer: int, x, mean, std, g, act, ld_act: int, idx, partials, stride: int, off_w: int, off_b: int,
-                  dims: Dims) -> None:
-    check(load().b200dp_tc_conv_wgrad(layer, _p(x), int(x.dtype == torch.uint8), mean, std, _p(g), _p(act), ld_act,
-                                      _p(idx), _p(partials), stride, off_w, off_b, dims, _stream()), "tc_conv_wgrad")
-
-
 # ---- window-tile tcgen05 convolutions (csrc/tc_win.cu) ----
 def tcw_pack_floats(dims: Dims) -> int:
     n = int(load().b200dp_tcw_pack_floats(dims))
@@ -199,6 +174,16 @@ def tcw_conv2_fwd(p1, wpack, b, p2, idx2, dims: Dims) -> None:
 def tcw_conv2_dgrad(dp2, p2, idx2, wpack, p1, g1, dims: Dims) -> None:
     check(load().b200dp_tcw_conv2_dgrad(_p(dp2), _p(p2), _p(idx2), _p(wpack), _p(p1), _p(g1), dims, _stream()),
           "tcw_conv2_dgrad")
+
+
+def tcw_conv_wgrad_num_partials(dims: Dims) -> int:
+    return int(load().b200dp_tcw_conv_wgrad_num_partials(dims))
+
+
+def tcw_conv_wgrad(layer: int, x, mean, std, g, act, ld_act: int, idx, partials, stride: int, off_w: int, off_b: int,
+                   dims: Dims) -> None:
+    check(load().b200dp_tcw_conv_wgrad(layer, _p(x), int(x.dtype == torch.uint8), mean, std, _p(g), _p(act), ld_act,
+                                       _p(idx), _p(partials), stride, off_w, off_b, dims, _stream()), "tcw_conv_wgrad")
 
 
 def linear_fwd(x, w, b, y, act: int) -> None:

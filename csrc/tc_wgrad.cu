@@ -1,0 +1,321 @@
+// Convolution weight gradients on tcgen05 (kind::f16, bf16 operands, fp32 accumulation in tensor memory) with both
+// operands read in place (MN-major, no swizzle).  (MN-major without swizzle is a 16-bit layout: with tf32 operands the
+// tensor core only accepts the SWIZZLE_128B_BASE32B form, whose 4-row swizzle phase a tap shift would break.)
+//
+//   dW[oc][ic][ky][kx] = sum_img sum_pos dZ[img][oc][pos] * X[img][ic][pos + ky*PITCH + kx],   db[oc] = sum dZ
+//
+// is a GEMM whose K dimension is the flat output position.  With the activations staged as
+// [channel group of 8][position][8 bf16] an MN-major no-swizzle descriptor reads them directly: the
+// 16-byte chunk is 8 channels of one position, 8 consecutive positions are one 8-row K group (LBO = 128 B),
+// the next channel group is SBO = (positions in the buffer) * 16 B away — and shifting the K origin by a tap
+// is a 16-byte-granular start-address change.  So:
+//   A (M = 128 rows)  "expanded" input channels c' -> X[plane(c')][pos + off(c')], plus one all-ones channel whose
+//                     accumulator row is the bias gradient
+//        layer 2: c' = (ic,kx)      (CIN*5+1 rows), the 5 ky taps are 5 start addresses, 5 accumulators
+//        layer 1: c' = (ic,ky,kx)   (CIN*25+1 rows), one accumulator (CIN is 1 or 3: everything fits in M)
+//   B (N = COUT cols) the un-pooled output gradient dZ (pool-bwd scatter + LeakyReLU' fused into the staging),
+//                     zero where no gradient flows, so the garbage columns of the PITCH-wide map add nothing
+// Accumulators stay in tensor memory across all images of the CTA; each CTA then writes ONE partial row that
+// b200dp_reduce_update sums in fixed order (deterministic, no atomics).
+//
+// Replaces the weight/bias-gradient half of the autograd backward of cnn.py:10-15 (train.py:49; cuDNN wgrad).
+//
+// CTA: warps 0-7 stage position chunks (double-buffered when shared memory allows), warp 8 issues the MMAs
+// (uniform control flow, one elected lane), warps 0-3 run the epilogue.
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace b200dp {
+
+constexpr int WG_THREADS = 288;
+constexpr int WG_STAGERS = 256;
+
+__device__ __forceinline__ uint64_t wg_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) |
+           ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
+}
+__device__ __forceinline__ uint32_t wg_pack_bf16(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_c, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_c), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ bool wg_elect() {
+    uint32_t p;
+    asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(p));
+    return p != 0;
+}
+
+template <int LAYER, int CIN, int COUT>
+struct WgCfg {
+    static constexpr bool FIRST = LAYER == 1;
+    static constexpr int PITCH = FIRST ? 32 : 14, PLANE = PITCH * PITCH;
+    static constexpr int OW = PITCH - 4, PW = OW / 2, PP = PW * PW;
+    static constexpr int NTAP = FIRST ? 1 : 5;                       // accumulators (ky taps kept as address shifts)
+    static constexpr int CA = FIRST ? CIN * 25 + 1 : CIN * 5 + 1;    // expanded channels + the ones channel
+    static constexpr int KGA = (CA + 7) / 8;                          // groups of 8 bf16 channels (16 bytes)
+    static_assert(CA <= 128, "expanded channels must fit the 128 accumulator rows");
+    static constexpr int NP = (COUT + 15) / 16 * 16, KGB = NP / 8;
+    static constexpr int NPOS = ((OW - 1) * PITCH + OW + 15) / 16 * 16;  // K extent of one image (16 positions per MMA)
+    static constexpr int P = FIRST ? 128 : NPOS;                      // positions per chunk
+    static constexpr int NCHUNK = (NPOS + P - 1) / P;
+    static constexpr int TAP_SPAN = FIRST ? 0 : 4 * PITCH;
+    static constexpr int PA = P + TAP_SPAN;                           // positions held by the A buffer
+    static constexpr int A_BYTES = 16 * PA * 16;                      // M = 128 addresses 16 channel groups of 8
+    static constexpr int B_BYTES = KGB * P * 16;
+    static constexpr int MAXOFF = 4 * PITCH + 4;
+    static constexpr int PLANE_PAD = (NCHUNK * P + TAP_SPAN + MAXOFF + 8 + 3) / 4 * 4;
+    static constexpr int PLANES_BYTES = CIN * PLANE_PAD * 4 + (FIRST ? CIN * 1024 * 4 : 0);
+    static constexpr int FIXED = 1024 + PLANES_BYTES + 64;
+    static constexpr int NBUF = (FIXED + 2 * (A_BYTES + B_BYTES) <= 232448) ? 2 : 1;
+    static constexpr size_t SMEM = FIXED + (size_t)NBUF * (A_BYTES + B_BYTES);
+    static_assert(SMEM <= 232448, "shared memory");
+    static constexpr int ACC_COLS = NTAP * NP;
+    static constexpr int TMEM_COLS = ACC_COLS <= 32 ? 32 : (ACC_COLS <= 64 ? 64 : (ACC_COLS <= 128 ? 128 : (ACC_COLS <= 256 ? 256 : 512)));
+    static_assert(ACC_COLS <= 512, "tensor memory");
+    // expanded channel -> (plane, offset inside the plane)
+    __host__ __device__ static constexpr int plane_of(int c) { return FIRST ? c / 25 : c / 5; }
+    __host__ __device__ static constexpr int off_of(int c) {
+        return FIRST ? ((c % 25) / 5) * PITCH + (c % 5) : c % 5;
+    }
+};
+
+struct WgArgs {
+    const void* x;            // layer 1: raw images [B][CIN][hw][hw] u8|f32;  layer 2: p1 [B][CIN][196]
+    int in_is_u8, in_hw; float mean, std;
+    const float* g;           // [B][COUT][PP] gradient at the pooled cells
+    const float* act; int ld_act;   // pooled activation for LeakyReLU' (nullable: g already carries it)
+    const uint8_t* idx;       // [B][COUT][PP] argmax inside the pool window
+    float* partials; int partial_stride, off_w, off_b;
+    int B, img_per_cta;
+};
+
+template <int LAYER, int CIN, int COUT>
+__global__ void __launch_bounds__(WG_THREADS, 1) wg_conv_kernel(const __grid_constant__ WgArgs a) {
+    using C = WgCfg<LAYER, CIN, COUT>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
+    uint8_t* sAB = base;                                               // [NBUF]{A: [32][PA][4], B: [KGB][P][4]}
+    float* sPl = reinterpret_cast<float*>(base + (size_t)C::NBUF * (C::A_BYTES + C::B_BYTES));   // [CIN][PLANE_PAD]
+    float* sRaw = sPl + CIN * C::PLANE_PAD;                            // layer 1 with 28x28 input: raw planes
+    uint64_t* bar_mem = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sPl) + C::PLANES_BYTES);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_mem + 5);
+    const uint32_t bars = smem_u32(bar_mem);
+    auto staged = [&](int b) { return bars + 8u * b; };                // stagers -> MMA warp (count 256)
+    auto drained = [&](int b) { return bars + 8u * (2 + b); };         // MMA warp -> stagers (tcgen05.commit)
+    const uint32_t acc_bar = bars + 8u * 4;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int img0 = blockIdx.x * a.img_per_cta;
+    const int nimg = max(0, min(a.img_per_cta, a.B - img0));
+    const int nchunks = nimg * C::NCHUNK;
+
+    if (tid == 0) {
+        for (int b = 0; b < 2; ++b) { mbar_init(staged(b), WG_STAGERS); mbar_init(drained(b), 1); }
+        mbar_init(acc_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 8) tmem_alloc(smem_u32(tmem_slot), C::TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp < 8) {
+        // ================= stagers =================
+        for (int ch = 0; ch < nchunks; ++ch) {
+            const int ii = ch / C::NCHUNK, ck = ch - ii * C::NCHUNK, img = img0 + ii;
+            const int b = C::NBUF == 2 ? (ch & 1) : 0;
+            if (ck == 0) {
+                // ---- the image's planes (normalised / up-sampled for the first layer), zero tail ----
+                asm volatile("bar.sync 1, %0;" ::"n"(WG_STAGERS) : "memory");      // previous image's expansion reads are done
+                if constexpr (C::FIRST) {
+                    const int hw = a.in_hw, n_in = hw * hw;
+                    if (hw == 32) {
+                        for (int i = tid; i < CIN * 1024; i += WG_STAGERS)
+                            sPl[(i >> 10) * C::PLANE_PAD + (i & 1023)] = load_pixel(a.x, a.in_is_u8, (long)img * CIN * 1024 + i, a.mean, a.std);
+                    } else {
+                        for (int i = tid; i < CIN * n_in; i += WG_STAGERS)
+                            sRaw[i] = load_pixel(a.x, a.in_is_u8, (long)img * CIN * n_in + i, a.mean, a.std);
+                        asm volatile("bar.sync 1, %0;" ::"n"(WG_STAGERS) : "memory");
+                        for (int c = 0; c < CIN; ++c) upsample32_plane(sRaw + c * n_in, hw, sPl + c * C::PLANE_PAD, tid, WG_STAGERS);
+                    }
+                } else {
+                    const float* src = (const float*)a.x + (long)img * CIN * C::PLANE;
+                    for (int i = tid; i < CIN * C::PLANE; i += WG_STAGERS) {
+                        const int c = i / C::PLANE;
+                        sPl[c * C::PLANE_PAD + (i - c * C::PLANE)] = __ldg(src + i);
+                    }
+                }
+                for (int i = tid; i < CIN * (C::PLANE_PAD - C::PLANE); i += WG_STAGERS) {
+                    const int c = i / (C::PLANE_PAD - C::PLANE);
+                    sPl[c * C::PLANE_PAD + C::PLANE + (i - c * (C::PLANE_PAD - C::PLANE))] = 0.f;
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(WG_STAGERS) : "memory");
+            }
+            // ---- wait until the tensor core has finished reading this buffer (chunk ch - NBUF) ----
+            if (ch >= C::NBUF) mbar_wait(drained(b), ((ch / C::NBUF) - 1) & 1);
+            uint4* sA = reinterpret_cast<uint4*>(sAB + (size_t)b * (C::A_BYTES + C::B_BYTES));
+            uint4* sB = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(sA) + C::A_BYTES);
+            const int p0 = ck * C::P;
+            // A: warp w expands channel groups w, w+8, ...; lanes run over positions (conflict-free 16-byte stores)
+            for (int cg = warp; cg < C::KGA; cg += 8) {
+                int off[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const int cc = cg * 8 + q;
+                    off[q] = cc < C::CA - 1 ? C::plane_of(cc) * C::PLANE_PAD + C::off_of(cc) + p0 : (cc == C::CA - 1 ? -1 : -2);
+                }
+                uint4* dst = sA + (size_t)cg * C::PA;
+#pragma unroll 2
+                for (int p = lane; p < C::PA; p += 32) {
+                    float v[8];
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) v[q] = off[q] >= 0 ? sPl[off[q] + p] : (off[q] == -1 ? 1.f : 0.f);
+                    dst[p] = make_uint4(wg_pack_bf16(v[0], v[1]), wg_pack_bf16(v[2], v[3]), wg_pack_bf16(v[4], v[5]),
+                                        wg_pack_bf16(v[6], v[7]));
+                }
+            }
+            // B: zero, then scatter the pooled gradients of this chunk's rows to their argmax positions
+            for (int i = tid; i < C::KGB * C::P; i += WG_STAGERS) sB[i] = make_uint4(0u, 0u, 0u, 0u);
+            asm volatile("bar.sync 1, %0;" ::"n"(WG_STAGERS) : "memory");
+            {
+                constexpr int ROWS = C::P / C::PITCH;                      // image rows per chunk (layer 1: 4; layer 2: all)
+                constexpr int PY_PER = C::FIRST ? ROWS / 2 : C::PW;        // pooled rows per chunk
+                const int py0 = C::FIRST ? ck * PY_PER : 0;
+                const int cells = COUT * PY_PER * C::PW;
+                __nv_bfloat16* sBh = reinterpret_cast<__nv_bfloat16*>(sB);
+                for (int i = tid; i < cells; i += WG_STAGERS) {
+                    const int oc = i / (PY_PER * C::PW), rem = i - oc * (PY_PER * C::PW);
+                    const int py = py0 + rem / C::PW, px = rem - (rem / C::PW) * C::PW;
+                    if (py < C::PW) {
+                        const long o = ((long)img * COUT + oc) * C::PP + py * C::PW + px;
+                        const int k = a.idx[o];
+                        float g = a.g[o];
+                        if (a.act) g *= leaky_grad_from_act(a.act[(long)img * a.ld_act + oc * C::PP + py * C::PW + px]);
+                        const int pos = (2 * py + (k >> 1)) * C::PITCH + 2 * px + (k & 1) - p0;
+                        sBh[((oc >> 3) * C::P + pos) * 8 + (oc & 7)] = __float2bfloat16_rn(g);
+                    }
+                }
+            }
+            fence_proxy_async_smem();
+            mbar_arrive(staged(b));
+        }
+    } else {
+        // ================= MMA issuer (warp 8): uniform loop, one elected lane =================
+        const bool leader = wg_elect();
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
+                               ((uint32_t)(C::NP >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);   // bf16 x bf16 -> f32, A and B MN-major
+        for (int ch = 0; ch < nchunks; ++ch) {
+            const int b = C::NBUF == 2 ? (ch & 1) : 0;
+            mbar_wait(staged(b), (ch / C::NBUF) & 1);
+            tc_fence_after();
+            const uint32_t sa = smem_u32(sAB + (size_t)b * (C::A_BYTES + C::B_BYTES)), sb = sa + C::A_BYTES;
+            const uint64_t adesc = wg_desc(sa, 128u, C::PA * 16u);      // LBO: next 8 positions; SBO: next channel group
+            const uint64_t bdesc = wg_desc(sb, 128u, C::P * 16u);
+            if (leader) {
+#pragma unroll 1
+                for (int j = 0; j < C::P / 16; ++j) {           // 16 positions (two 8-row K groups, LBO apart) per MMA
+#pragma unroll
+                    for (int t = 0; t < C::NTAP; ++t)
+                        umma_bf16(tmem + (uint32_t)(t * C::NP), adesc + (uint64_t)(t * C::PITCH + 16 * j), bdesc + (uint64_t)(16 * j),
+                                  idesc, (ch | j) != 0);
+                }
+                umma_commit(drained(b));
+                if (ch == nchunks - 1) umma_commit(acc_bar);
+            }
+            __syncwarp();
+        }
+    }
+
+    // ================= epilogue (warps 0-3): thread = accumulator row = expanded channel =================
+    if (warp < 4) {
+        float* row = a.partials + (long)blockIdx.x * a.partial_stride;
+        const int m = warp * 32 + lane;
+        if (nchunks > 0) {
+            mbar_wait(acc_bar, 0);
+            tc_fence_after();
+        }
+        constexpr int KW = CIN * 25;
+        // destination of row m inside dW[oc][ic][ky][kx] for tap t (layer 2: m = (ic,kx), t = ky)
+#pragma unroll 1
+        for (int t = 0; t < C::NTAP; ++t) {
+            int wofs = -1;
+            if (m < C::CA - 1) wofs = C::FIRST ? m : (m / 5) * 25 + t * 5 + (m % 5);
+            const bool is_bias = (m == C::CA - 1) && t == 0;
+#pragma unroll 1
+            for (int n0 = 0; n0 < C::NP; n0 += 16) {
+                uint32_t v[16];
+                if (nchunks > 0) {
+                    tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * C::NP + n0), v);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] = 0u;
+                }
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const int n = n0 + j;
+                    if (n < COUT) {
+                        if (wofs >= 0) row[a.off_w + n * KW + wofs] = __uint_as_float(v[j]);
+                        else if (is_bias) row[a.off_b + n] = __uint_as_float(v[j]);
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8) {
+        tc_fence_after();
+        tmem_dealloc(tmem, C::TMEM_COLS);
+    }
+}
+
+template <int LAYER, int CIN, int COUT>
+static int wg_launch(const WgArgs& a, int rows, cudaStream_t s) {
+    using C = WgCfg<LAYER, CIN, COUT>;
+    auto kern = wg_conv_kernel<LAYER, CIN, COUT>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200DP_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+        attr_set = true;
+    }
+    kern<<<rows, WG_THREADS, C::SMEM, s>>>(a);
+    B200DP_CHECK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace b200dp
+
+using namespace b200dp;
+
+extern "C" int b200dp_tcw_conv_wgrad_num_partials(b200dp_dims d) {
+    int n = (d.batch + 1) / 2;
+    if (n > 128) n = 128;
+    return n < 1 ? 1 : n;
+}
+
+extern "C" int b200dp_tcw_conv_wgrad(int layer, const void* x, int in_is_u8, float mean, float std, const float* g,
+                                     const float* act, int ld_act, const uint8_t* idx, float* partials,
+                                     int partial_stride, int off_w, int off_b, b200dp_dims d, b200dp_stream_t s) {
+    const int rows = b200dp_tcw_conv_wgrad_num_partials(d);
+    const int ipc = (d.batch + rows - 1) / rows;
+    WgArgs a{x, in_is_u8, d.in_hw, mean, std, g, act, ld_act, idx, partials, partial_stride, off_w, off_b, d.batch, ipc};
+    if (layer == 2) {
+        if (d.c1 == 24 && d.c2 == 64) return wg_launch<2, 24, 64>(a, rows, (cudaStream_t)s);
+        if (d.c1 == 6 && d.c2 == 16) return wg_launch<2, 6, 16>(a, rows, (cudaStream_t)s);
+    } else if (layer == 1) {
+        B200DP_REQUIRE(d.in_hw == 28 || d.in_hw == 32, "in_hw must be 28 or 32");
+        if (d.in_ch == 3 && d.c1 == 24) return wg_launch<1, 3, 24>(a, rows, (cudaStream_t)s);
+        if (d.in_ch == 1 && d.c1 == 6) return wg_launch<1, 1, 6>(a, rows, (cudaStream_t)s);
+    }
+    B200DP_REQUIRE(false, "unsupported layer / channel combination");
+}

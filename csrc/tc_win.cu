@@ -29,8 +29,10 @@
 
 namespace b200dp {
 
-constexpr int WIN_THREADS = 320;
-constexpr int WIN_STAGERS = 256;
+constexpr int WIN_NMMA = 4;                          // MMA-issuing warps, each owns the accumulators ai % 4 == m
+constexpr int WIN_WORKERS = 16;                      // staging + epilogue warps (4 per tensor-memory lane quadrant)
+constexpr int WIN_THREADS = 32 * (WIN_WORKERS + WIN_NMMA + 1);
+constexpr int WIN_STAGERS = 32 * 16;
 
 // K-major / MN-major operand descriptor without swizzle (layout type 0), strides in bytes.
 __device__ __forceinline__ uint64_t nosw_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
@@ -89,7 +91,10 @@ struct WinArgs {
     const float* mask;        // DGRAD: p1 [B][CIN][196] (LeakyReLU' of layer 1)
     int B, in_is_u8, in_hw, out_img_stride, ld_act;
     float mean, std;
+    long long* dbg;           // profiling aid (nullable): CTA 0 writes clock64() stamps of its phases to dbg[0..16)
 };
+static long long* g_win_dbg = nullptr;
+#define WIN_STAMP(i) do { if (a.dbg && blockIdx.x == 0 && (threadIdx.x & 31) == 0) a.dbg[i] = clock64(); } while (0)
 
 // ---------------------------------------------------------------------------------------------------
 // staging (warps 0-7)
@@ -98,6 +103,7 @@ template <class C, int CIN>
 __device__ __forceinline__ void win_stage_fwd2(const WinArgs& a, int img, float* sImg, int tid) {
     // NCHW planes -> [cg][pixel][4]: one float4 store per (pixel, channel group), 4 coalesced plane reads
     const float* src = (const float*)a.x + (long)img * CIN * 196;
+#pragma unroll 4
     for (int i = tid; i < C::KG * C::NPIX; i += WIN_STAGERS) {
         const int cg = i / C::NPIX, p = i - cg * C::NPIX;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -115,26 +121,39 @@ __device__ __forceinline__ void win_stage_fwd2(const WinArgs& a, int img, float*
 template <class C, int CIN>
 __device__ __forceinline__ void win_stage_fwd1(const WinArgs& a, int img, float* sImg, float* sRaw, float* sUp, int tid) {
     const int hw = a.in_hw, n_in = hw * hw;
-    for (int i = tid; i < CIN * n_in; i += WIN_STAGERS)
-        sRaw[i] = load_pixel(a.x, a.in_is_u8, (long)img * CIN * n_in + i, a.mean, a.std);
-    asm volatile("bar.sync 1, %0;" ::"n"(WIN_STAGERS) : "memory");
-    for (int c = 0; c < CIN; ++c) {
-        upsample32_plane(sRaw + c * n_in, hw, sUp + c * C::PLANE_PAD, tid, WIN_STAGERS);
-        if (tid < 8) sUp[c * C::PLANE_PAD + 1024 + tid] = 0.f;          // kx overrun of the last pixel
+    if (hw == 32) {                      // no resampling: normalise straight into the padded planes
+        for (int i = tid; i < CIN * 1024; i += WIN_STAGERS)
+            sUp[(i >> 10) * C::PLANE_PAD + (i & 1023)] = load_pixel(a.x, a.in_is_u8, (long)img * CIN * 1024 + i, a.mean, a.std);
+    } else {
+        for (int i = tid; i < CIN * n_in; i += WIN_STAGERS)
+            sRaw[i] = load_pixel(a.x, a.in_is_u8, (long)img * CIN * n_in + i, a.mean, a.std);
+        asm volatile("bar.sync 1, %0;" ::"n"(WIN_STAGERS) : "memory");
+        for (int c = 0; c < CIN; ++c) upsample32_plane(sRaw + c * n_in, hw, sUp + c * C::PLANE_PAD, tid, WIN_STAGERS);
     }
+    if (tid < 8 * CIN) sUp[(tid >> 3) * C::PLANE_PAD + 1024 + (tid & 7)] = 0.f;      // kx overrun of the last pixels
     asm volatile("bar.sync 1, %0;" ::"n"(WIN_STAGERS) : "memory");
-    // kx-expansion: staged channel c' = ic*5 + kx holds X[ic][p + kx]
-    for (int i = tid; i < C::KG * C::NPIX; i += WIN_STAGERS) {
-        const int cg = i / C::NPIX, p = i - cg * C::NPIX;
-        float v[4] = {0.f, 0.f, 0.f, 0.f};
-        if (p < 1024) {
+    // kx-expansion: staged channel c' = ic*5 + kx holds X[ic][p + kx].  A thread keeps one channel group, so the
+    // four plane offsets are loop invariants; consecutive lanes take consecutive pixels (conflict-free).
+    constexpr int TPG = WIN_STAGERS / C::KG;                 // threads per channel group
+    static_assert(WIN_STAGERS % C::KG == 0, "stagers must split evenly over the channel groups");
+    const int cg = tid / TPG, p0 = tid - cg * TPG;
+    int off[4];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int cc = cg * 4 + q;
-                if (cc < CIN * 5) { const int ic = cc / 5, kx = cc - ic * 5; v[q] = sUp[ic * C::PLANE_PAD + p + kx]; }
-            }
+    for (int q = 0; q < 4; ++q) {
+        const int cc = cg * 4 + q;
+        off[q] = cc < CIN * 5 ? (cc / 5) * C::PLANE_PAD + (cc % 5) : -1;
+    }
+    float4* dst = reinterpret_cast<float4*>(sImg) + (size_t)cg * C::NPIX;
+#pragma unroll 4
+    for (int p = p0; p < C::NPIX; p += TPG) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (p < 1024) {
+            if (off[0] >= 0) v.x = sUp[off[0] + p];
+            if (off[1] >= 0) v.y = sUp[off[1] + p];
+            if (off[2] >= 0) v.z = sUp[off[2] + p];
+            if (off[3] >= 0) v.w = sUp[off[3] + p];
         }
-        reinterpret_cast<float4*>(sImg)[i] = make_float4(v[0], v[1], v[2], v[3]);
+        dst[p] = v;
     }
     asm volatile("bar.sync 1, %0;" ::"n"(WIN_STAGERS) : "memory");     // sRaw / sUp are reused by the next image
 }
@@ -155,6 +174,47 @@ __device__ __forceinline__ void win_stage_dgrad(const WinArgs& a, int img, float
 }
 
 // ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool elect_one() {
+    uint32_t p;
+    asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(p));
+    return p != 0;
+}
+
+template <class C, int M>
+__device__ __forceinline__ void win_issue(uint32_t tmem, uint32_t s_img, uint32_t s_w, uint32_t bars, int nimg) {
+    const bool leader = elect_one();
+    const uint32_t idesc = idesc_tf32(C::NP, 0, 0);
+    const uint64_t adesc0 = nosw_desc(s_img, C::NPIX * 16u, C::PITCH * 16u);
+    const uint64_t bdesc0 = nosw_desc(s_w, C::NP * 16u, 128u);
+    const uint32_t acc_bar = bars + 8u * (2 * C::RING);
+#pragma unroll 1
+    for (int t = 0; t < C::NTAP; ++t) {
+        const int s = t % C::RING;
+        mbar_wait(bars + 8u * s, (t / C::RING) & 1);
+        tc_fence_after();
+        const uint64_t at = adesc0 + (uint64_t)C::tap_shift(t);                 // the address field counts 16-byte units
+        const uint64_t bt = bdesc0 + (uint64_t)(s * (C::WB >> 4));
+        const uint32_t acc = t != 0;
+        if (leader) {
+#pragma unroll
+            for (int ai = M; ai < C::G * C::NT; ai += WIN_NMMA) {
+                const int g = ai / C::NT, tl = ai % C::NT;
+                if (g < nimg) {
+                    const int r0 = (tl / C::NTC) * 16, c0 = (tl % C::NTC) * 8;
+                    const uint64_t ag = at + (uint64_t)((g * C::IMG_BYTES + (r0 * C::PITCH + c0) * 16) >> 4);
+#pragma unroll
+                    for (int ks = 0; ks < C::KSTEPS; ++ks)
+                        umma_tf32(tmem + (uint32_t)(ai * C::NP), ag + (uint64_t)(ks * 2 * C::NPIX),
+                                  bt + (uint64_t)(ks * 2 * C::NP), idesc, ks != 0 ? 1u : acc);
+                }
+            }
+            umma_commit(bars + 8u * (C::RING + s));
+            if (t == C::NTAP - 1) umma_commit(acc_bar);
+        }
+        __syncwarp();
+    }
+}
+
 template <int KIND, int CIN, int COUT>
 __global__ void __launch_bounds__(WIN_THREADS, 1) win_conv_kernel(const __grid_constant__ WinArgs a) {
     using C = WinCfg<KIND, CIN, COUT>;
@@ -173,28 +233,30 @@ __global__ void __launch_bounds__(WIN_THREADS, 1) win_conv_kernel(const __grid_c
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int img0 = blockIdx.x * C::G;
     const int nimg = min(C::G, a.B - img0);
+    if (tid == 0) WIN_STAMP(0);
 
     if (tid == 0) {
-        for (int s = 0; s < C::RING; ++s) { mbar_init(w_full(s), 1); mbar_init(w_empty(s), 1); }
-        mbar_init(acc_bar, 1);
+        for (int s = 0; s < C::RING; ++s) { mbar_init(w_full(s), 1); mbar_init(w_empty(s), WIN_NMMA); }
+        mbar_init(acc_bar, WIN_NMMA);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 8) tmem_alloc(smem_u32(tmem_slot), C::TMEM_COLS);
+    if (warp == WIN_WORKERS) tmem_alloc(smem_u32(tmem_slot), C::TMEM_COLS);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    if (tid == 0) WIN_STAMP(1);
 
     auto load_tap = [&](int t) {
         const int s = t % C::RING;
         mbar_expect_tx(w_full(s), C::WB);
         tma_bulk_load(smem_u32(sW + (size_t)s * C::WB), a.wpack + (size_t)t * (C::WB / 4), C::WB, w_full(s));
     };
-    if (warp == 9) {
+    if (warp == WIN_WORKERS + WIN_NMMA) {
         // ================= weight ring producer (one lane): fill the ring while the images are staged =================
         if (lane == 0)
             for (int t = 0; t < C::RING && t < C::NTAP; ++t) load_tap(t);
-    } else if (warp < 8) {
+    } else if (warp < WIN_WORKERS) {
         // ================= stage the CTA's images =================
         for (int g = 0; g < nimg; ++g) {
             float* dst = sImg + (size_t)g * (C::IMG_BYTES / 4);
@@ -203,58 +265,48 @@ __global__ void __launch_bounds__(WIN_THREADS, 1) win_conv_kernel(const __grid_c
             else win_stage_dgrad<C, COUT>(a, img0 + g, dst, tid);
         }
         fence_proxy_async_smem();          // generic-proxy stores -> visible to the tensor core's reads
+        if (tid == 0) WIN_STAMP(2);
     }
     __syncthreads();
+    if (tid == 0) WIN_STAMP(3);
 
-    if (warp == 9) {
+    if (warp == WIN_WORKERS + WIN_NMMA) {
         if (lane == 0)
             for (int t = C::RING; t < C::NTAP; ++t) {          // refill a stage once its MMAs have completed
                 mbar_wait(w_empty(t % C::RING), ((t / C::RING) - 1) & 1);
                 load_tap(t);
             }
-    } else if (warp == 8) {
-        // ================= MMA issuer =================
+    } else if (warp >= WIN_WORKERS) {
+        // ================= MMA issuers: warp WIN_WORKERS+m owns the accumulators (image g, tile tl) with (g*NT+tl) % 4 == m.
+        // The loop is warp-uniform (descriptors live in uniform registers); one elected lane issues. =================
         tc_fence_after();
-        const uint32_t idesc = idesc_tf32(C::NP, 0, 0);
-        const uint32_t img_base = smem_u32(sImg);
-        for (int t = 0; t < C::NTAP; ++t) {
-            const int s = t % C::RING;
-            mbar_wait(w_full(s), (t / C::RING) & 1);
-            tc_fence_after();
-            if (lane == 0) {
-                const uint32_t wb = smem_u32(sW + (size_t)s * C::WB);
-                const uint32_t shift = (uint32_t)C::tap_shift(t) * 16u;
-                for (int g = 0; g < nimg; ++g) {
-#pragma unroll
-                    for (int tl = 0; tl < C::NT; ++tl) {
-                        const int r0 = (tl / C::NTC) * 16, c0 = (tl % C::NTC) * 8;
-                        const uint32_t a0 = img_base + (uint32_t)g * C::IMG_BYTES + (uint32_t)(r0 * C::PITCH + c0) * 16u + shift;
-                        const uint32_t d = tmem + (uint32_t)((g * C::NT + tl) * C::NP);
-#pragma unroll
-                        for (int ks = 0; ks < C::KSTEPS; ++ks) {
-                            const uint32_t aa = a0 + (uint32_t)ks * 2u * C::NPIX * 16u, bb = wb + (uint32_t)ks * 2u * C::NP * 16u;
-                            umma_tf32(d, nosw_desc(aa, C::NPIX * 16u, C::PITCH * 16u), nosw_desc(bb, C::NP * 16u, 128u), idesc, (t | ks) != 0);
-                        }
-                    }
-                }
-                umma_commit(w_empty(s));
-                if (t == C::NTAP - 1) umma_commit(acc_bar);
-            }
-            __syncwarp();
+        const uint32_t sw = smem_u32(sW), si = smem_u32(sImg);
+        switch (warp - WIN_WORKERS) {
+            case 0: win_issue<C, 0>(tmem, si, sw, bars, nimg); break;
+            case 1: win_issue<C, 1>(tmem, si, sw, bars, nimg); break;
+            case 2: win_issue<C, 2>(tmem, si, sw, bars, nimg); break;
+            default: win_issue<C, 3>(tmem, si, sw, bars, nimg); break;
         }
-    } else if (warp < 4) {
-        // ================= epilogue: thread = pixel (row 4*warp + lane/8, column lane%8 of the tile) =================
+        if (warp == WIN_WORKERS) WIN_STAMP(4);
+    } else {
+        // ================= epilogue (16 warps; a lone warp issues a dependent instruction only every ~5 cycles, so the work is spread
+        // over four warps per scheduler): warp w reads TMEM lane quadrant w%4 (rows 4q..4q+3 of a tile; thread =
+        // pixel: row 4q + lane/8, column lane%8); items are dealt round-robin to the four warps of a quadrant =================
         mbar_wait(acc_bar, 0);
         tc_fence_after();
-        const int lr = 4 * warp + (lane >> 3), lc = lane & 7;
-        for (int g = 0; g < nimg; ++g) {
+        if (tid == 0) WIN_STAMP(5);
+        const int q = warp & 3;
+        const int lr = 4 * q + (lane >> 3), lc = lane & 7;
+        constexpr int NCH = C::NP / 16;                     // work item = (accumulator, 16-column chunk)
+#pragma unroll 1
+        for (int item = warp >> 2; item < nimg * C::NT * NCH; item += WIN_WORKERS / 4) {
+            const int ai = item / NCH, n0 = (item - ai * NCH) * 16;
+            const int g = ai / C::NT, tl = ai - g * C::NT;
             const int img = img0 + g;
-#pragma unroll 1
-            for (int tl = 0; tl < C::NT; ++tl) {
+            {
                 const int r = (tl / C::NTC) * 16 + lr, c = (tl % C::NTC) * 8 + lc;
-                const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)((g * C::NT + tl) * C::NP);
-#pragma unroll 1
-                for (int n0 = 0; n0 < C::NP; n0 += 16) {
+                const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(ai * C::NP);
+                {
                     uint32_t v[16];
                     tmem_ld16(taddr + (uint32_t)n0, v);
                     if constexpr (KIND == WIN_DGRAD) {
@@ -273,24 +325,35 @@ __global__ void __launch_bounds__(WIN_THREADS, 1) win_conv_kernel(const __grid_c
                         const int win = ((r & 1) << 1) | (c & 1);
                         const int py = r >> 1, px = c >> 1;
                         const bool writer = win == 0 && py < PW && px < PW;
+                        // all 16 columns' shuffles are independent: issue them back to back, store afterwards
+                        float best[16];
+                        int bi[16];
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
-                            const int n = n0 + j;
-                            if (n < COUT) {                                   // warp-uniform
-                                float best = leaky(__uint_as_float(v[j]) + __ldg(a.bias + n));
-                                int bi = win;
-                                {   // columns: lane ^ 1; rows: lane ^ 8.  First maximum wins (torch's tie rule)
-                                    float ov = __shfl_xor_sync(0xffffffffu, best, 1);
-                                    int oi = __shfl_xor_sync(0xffffffffu, bi, 1);
-                                    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
-                                    ov = __shfl_xor_sync(0xffffffffu, best, 8);
-                                    oi = __shfl_xor_sync(0xffffffffu, bi, 8);
-                                    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
-                                }
-                                if (writer) {
-                                    a.out[(long)img * a.out_img_stride + n * PP + py * PW + px] = best;
-                                    if (a.idx) a.idx[((long)img * COUT + n) * PP + py * PW + px] = (uint8_t)bi;
-                                }
+                            best[j] = leaky(__uint_as_float(v[j]) + ((n0 + j < COUT) ? __ldg(a.bias + n0 + j) : 0.f));
+                            bi[j] = win;
+                        }
+#pragma unroll
+                        for (int o = 1; o <= 8; o <<= 3) {      // columns: lane ^ 1; rows: lane ^ 8.  First maximum wins (torch)
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                const float ov = __shfl_xor_sync(0xffffffffu, best[j], o);
+                                const int oi = __shfl_xor_sync(0xffffffffu, bi[j], o);
+                                const bool take = ov > best[j] || (ov == best[j] && oi < bi[j]);
+                                best[j] = take ? ov : best[j];
+                                bi[j] = take ? oi : bi[j];
+                            }
+                        }
+                        if (writer) {
+                            float* po = a.out + (long)img * a.out_img_stride + py * PW + px;
+#pragma unroll
+                            for (int j = 0; j < 16; ++j)
+                                if (n0 + j < COUT) po[(n0 + j) * PP] = best[j];
+                            if (a.idx) {
+                                uint8_t* pi = a.idx + (long)img * COUT * PP + py * PW + px;
+#pragma unroll
+                                for (int j = 0; j < 16; ++j)
+                                    if (n0 + j < COUT) pi[(n0 + j) * PP] = (uint8_t)bi[j];
                             }
                         }
                     }
@@ -298,11 +361,13 @@ __global__ void __launch_bounds__(WIN_THREADS, 1) win_conv_kernel(const __grid_c
             }
         }
     }
+    if (tid == 0) WIN_STAMP(6);
     tc_fence_before();
     __syncthreads();
-    if (warp == 8) {
+    if (warp == WIN_WORKERS) {
         tc_fence_after();
         tmem_dealloc(tmem, C::TMEM_COLS);
+        WIN_STAMP(7);
     }
 }
 
@@ -345,7 +410,9 @@ static int win_launch(const WinArgs& a, cudaStream_t s) {
         B200DP_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
         attr_set = true;
     }
-    kern<<<(a.B + C::G - 1) / C::G, WIN_THREADS, C::SMEM, s>>>(a);
+    WinArgs b = a;
+    b.dbg = g_win_dbg;
+    kern<<<(a.B + C::G - 1) / C::G, WIN_THREADS, C::SMEM, s>>>(b);
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }
@@ -371,6 +438,10 @@ static bool pack_layout(b200dp_dims d, PackLayout& L) {
 }  // namespace b200dp
 
 using namespace b200dp;
+
+// Profiling aid: while set, CTA 0 of every window-tile launch writes clock64() stamps to dbg[0..16)
+// (0 start, 1 set-up done, 2 staged, 3 after barrier, 4 MMAs issued, 5 accumulators ready, 6 epilogue done, 7 end).
+extern "C" void b200dp_tcw_set_debug(long long* dbg) { g_win_dbg = dbg; }
 
 extern "C" long b200dp_tcw_pack_floats(b200dp_dims d) {
     PackLayout L;

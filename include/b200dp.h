@@ -107,33 +107,19 @@ int b200dp_tc_gemm_group(const b200dp_tc_problem* probs, int count, b200dp_strea
 /* Profiling aid: same launch; CTA 0 records clock64() stamps of its pipeline phases in dbg[0..32). */
 int b200dp_tc_gemm_group_timed(const b200dp_tc_problem* probs, int count, long long* dbg, b200dp_stream_t s);
 
-/* Convolutions as implicit GEMMs on tcgen05 (tf32, TMEM accumulators; csrc/tc_conv.cu), same
- * tensors and semantics as the CUDA-core entry points above / below.  Supported geometries:
- * (in_ch,c1,c2) = (1,6,16) and (3,24,64).
- *   b200dp_tc_conv1_fwd / b200dp_tc_conv2_fwd : drop-in for b200dp_conv1_fwd / b200dp_conv2_fwd
- *   b200dp_tc_conv2_dgrad : g1[B][c1][196] = (pool2-bwd, LeakyReLU-bwd, conv2 dgrad) * LeakyReLU'(p1)
- *   b200dp_tc_conv_wgrad  : layer 2: dW2/db2 from (x = p1, g = dp2, act = p2, idx = idx2)
- *                           layer 1: dW1/db1 from (x = raw images, g = g1, act = NULL, idx = idx1)
- *     written as partial rows [b200dp_tc_conv_wgrad_num_partials(d)][partial_stride] at columns
- *     off_w / off_b (summed in fixed order by b200dp_reduce_update).
- * Replaces cnn.py:10-15 and their backward (train.py:49); cuDNN in the reference. */
-int b200dp_tc_conv1_fwd(const void* x, int in_is_u8, float mean, float std, const float* w, const float* b,
-                        float* p1, uint8_t* idx1, b200dp_dims d, b200dp_stream_t s);
-int b200dp_tc_conv2_fwd(const float* p1, const float* w, const float* b, float* p2, uint8_t* idx2,
-                        b200dp_dims d, b200dp_stream_t s);
-int b200dp_tc_conv2_dgrad(const float* dp2, const float* p2, const uint8_t* idx2, const float* w2,
-                          const float* p1, float* g1, b200dp_dims d, b200dp_stream_t s);
-int b200dp_tc_conv_wgrad_num_partials(b200dp_dims d);
-int b200dp_tc_conv_wgrad(int layer, const void* x, int in_is_u8, float mean, float std, const float* g,
-                         const float* act, int ld_act, const uint8_t* idx, float* partials,
-                         int partial_stride, int off_w, int off_b, b200dp_dims d, b200dp_stream_t s);
-
 /* "Window-tile" convolutions (csrc/tc_win.cu): tcgen05 implicit GEMM that reads the staged image in place —
  * an accumulator tile is a 16x8-pixel window addressed by a no-swizzle K-major descriptor, a filter tap is a
- * start-address shift, so no im2col operand is ever written.  Same tensors and semantics as the
- * b200dp_tc_conv* entry points, except that the weights come pre-packed: call b200dp_tcw_pack_weights once
- * per step (after the optimizer update) into a scratch of b200dp_tcw_pack_floats(d) floats; it packs the
- * first layer's forward panels, the second layer's forward panels and its flipped data-gradient panels.
+ * start-address shift, so no im2col operand is ever written (kind::tf32, fp32 accumulation in tensor memory).
+ * Same tensors and semantics as b200dp_conv1_fwd / b200dp_conv2_fwd, except that the weights come
+ * pre-packed: call b200dp_tcw_pack_weights once per step (after the optimizer update) into a scratch of
+ * b200dp_tcw_pack_floats(d) floats; it packs the first layer's forward panels, the second layer's forward
+ * panels and its flipped data-gradient panels.
+ *   b200dp_tcw_conv2_dgrad : g1[B][c1][196] = (pool2-bwd, LeakyReLU-bwd, conv2 dgrad) * LeakyReLU'(p1)
+ *   b200dp_tcw_conv_wgrad  (csrc/tc_wgrad.cu; kind::f16 on bf16 operands, both MN-major and read in place):
+ *                           layer 2: dW2/db2 from (x = p1, g = dp2, act = p2, idx = idx2)
+ *                           layer 1: dW1/db1 from (x = raw images, g = g1, act = NULL, idx = idx1)
+ *     written as partial rows [b200dp_tcw_conv_wgrad_num_partials(d)][partial_stride] at columns
+ *     off_w / off_b (summed in fixed order by b200dp_reduce_update).
  * Supported geometries: (in_ch,c1,c2) = (1,6,16) and (3,24,64).
  * Replaces cnn.py:10-15 and their backward (train.py:49); cuDNN in the reference. */
 long b200dp_tcw_pack_floats(b200dp_dims d);
@@ -144,6 +130,13 @@ int b200dp_tcw_conv2_fwd(const float* p1, const float* wpack, const float* b, fl
                          b200dp_dims d, b200dp_stream_t s);
 int b200dp_tcw_conv2_dgrad(const float* dp2, const float* p2, const uint8_t* idx2, const float* wpack,
                            const float* p1, float* g1, b200dp_dims d, b200dp_stream_t s);
+int b200dp_tcw_conv_wgrad_num_partials(b200dp_dims d);
+int b200dp_tcw_conv_wgrad(int layer, const void* x, int in_is_u8, float mean, float std, const float* g,
+                          const float* act, int ld_act, const uint8_t* idx, float* partials,
+                          int partial_stride, int off_w, int off_b, b200dp_dims d, b200dp_stream_t s);
+/* Profiling aid: while dbg != NULL, CTA 0 of every window-tile launch writes clock64() stamps of its phases
+ * (start, set-up, staged, barrier, MMAs issued, accumulators ready, epilogue done, end) to dbg[0..8). */
+void b200dp_tcw_set_debug(long long* dbg);
 
 /* Fused convolution backward for one step: pool2-bwd + leaky-bwd + conv2 dgrad
  * + conv2 wgrad/bgrad + pool1-bwd + leaky-bwd + conv1 wgrad/bgrad (no conv1

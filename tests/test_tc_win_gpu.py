@@ -105,3 +105,60 @@ def test_tcw_conv2_dgrad(cfg, b):
                            P1.detach().float().contiguous(), g1, d)
     torch.cuda.synchronize()
     assert _close(g1, z1.grad, 2e-2)
+
+
+@pytest.mark.parametrize("cfg", CFGS)
+@pytest.mark.parametrize("b", [1, 2, 37, 256])
+def test_tcw_conv2_wgrad(cfg, b):
+    """wgrad/bgrad of conv2 against autograd through conv2 -> LeakyReLU -> max-pool."""
+    native = _native()
+    torch.manual_seed(4)
+    dev = "cuda"
+    md = LeNet(cfg).to(dev).double()
+    conv = md.ConvNet[4]
+    P1 = F.leaky_relu(torch.randn(b, cfg.c1, 14, 14, device=dev, dtype=torch.float64), 0.2)
+    p2, idx2, _ = _pool(conv(P1))
+    dp2 = torch.randn_like(p2)
+    conv.zero_grad()
+    p2.backward(dp2)
+    d = _dims(native, cfg, b)
+    n_rows = native.tcw_conv_wgrad_num_partials(d)
+    wn = cfg.c2 * cfg.c1 * 25
+    partials = torch.zeros(n_rows, wn + cfg.c2 + 8, device=dev)
+    native.tcw_conv_wgrad(2, P1.detach().float().contiguous(), 0.0, 1.0, dp2.float().contiguous(),
+                          p2.detach().float().contiguous(), cfg.c2 * 25, idx2, partials, partials.shape[1], 0, wn, d)
+    torch.cuda.synchronize()
+    rows = partials.double().sum(0)
+    assert _close(rows[:wn].view_as(conv.weight), conv.weight.grad, 2e-2)
+    assert _close(rows[wn: wn + cfg.c2], conv.bias.grad, 2e-2)
+    assert (partials[:, wn + cfg.c2:] == 0).all()
+
+
+@pytest.mark.parametrize("cfg", CFGS)
+@pytest.mark.parametrize("b,u8", [(1, True), (2, True), (37, True), (256, True), (5, False)])
+def test_tcw_conv1_wgrad(cfg, b, u8):
+    native = _native()
+    torch.manual_seed(3)
+    dev = "cuda"
+    md = LeNet(cfg).to(dev).double()
+    conv = md.ConvNet[1]
+    if u8:
+        x = torch.randint(0, 256, (b, cfg.in_ch, cfg.in_hw, cfg.in_hw), dtype=torch.uint8, device=dev)
+        xf = (x.double().div(255) - MEAN) / STD
+    else:
+        x = torch.randn(b, cfg.in_ch, cfg.in_hw, cfg.in_hw, device=dev)
+        xf = x.double()
+    z = conv(md.ConvNet[0](xf))
+    _, idx1, flat = _pool(z)
+    g1 = torch.randn(b, cfg.c1, 14, 14, device=dev, dtype=torch.float64)      # gradient at the pooled cells
+    dz = torch.zeros_like(z).view(b, cfg.c1, -1).scatter_(2, flat.view(b, cfg.c1, -1), g1.view(b, cfg.c1, -1)).view_as(z)
+    gw, gb = torch.autograd.grad(z, [conv.weight, conv.bias], grad_outputs=dz)
+    d = _dims(native, cfg, b)
+    n_rows = native.tcw_conv_wgrad_num_partials(d)
+    wn = cfg.c1 * cfg.in_ch * 25
+    partials = torch.zeros(n_rows, wn + cfg.c1 + 3, device=dev)
+    native.tcw_conv_wgrad(1, x, MEAN, STD, g1.float().contiguous(), None, 0, idx1, partials, partials.shape[1], 0, wn, d)
+    torch.cuda.synchronize()
+    rows = partials.double().sum(0)
+    assert _close(rows[:wn].view_as(gw), gw, 2e-2)
+    assert _close(rows[wn: wn + cfg.c1], gb, 2e-2)
