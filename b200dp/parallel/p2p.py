@@ -34,8 +34,11 @@ from ..ops import native
 FLAG_GRAIN = 32   # csrc/reduce_update.cu RU_FLAG_GRAIN
 MAX_WORLD = 8
 ALGO_CODES = {"oneshot": 0, "twoshot": 1, "nvls": 2}
-# measured cross-over on 8xB200 (profiles/allreduce_sweep.md): below this a single exchange wins
-ONESHOT_MAX_BYTES = 512 * 1024
+# Measured cross-over (profiles/allreduce_sweep.md).  One-shot pulls (world-1) x bytes into every rank but needs a
+# single handshake; two-shot / NVLS move 2(world-1)/world x bytes with two.  With 2 ranks the byte counts are
+# equal, so one-shot always wins; at 8 ranks it wins up to 4 MB.
+def oneshot_max_bytes(world: int) -> int:
+    return (1 << 62) if world <= 2 else (32 << 20) // world
 
 
 class P2PComm:
@@ -63,7 +66,8 @@ class P2PComm:
         if world > 1:
             # CUDA IPC is the default; torch symmetric memory is only needed (and only tried) for the
             # multicast alias that NVLS requires
-            want_symm = transport == "symm" or (transport == "auto" and algo == "nvls")
+            big = arena_len * 4 > oneshot_max_bytes(world)       # some bucket may want the multicast (NVLS) path
+            want_symm = transport == "symm" or (transport == "auto" and (algo == "nvls" or (algo == "auto" and big)))
             if not (want_symm and self._setup_symm()):
                 self._setup_ipc()
             for r in range(world):
@@ -113,7 +117,7 @@ class P2PComm:
         """The ``b200dp_comm`` to pass for a bucket of this size (algorithm chosen per bucket)."""
         algo = self.algo
         if algo == "auto":
-            algo = "oneshot" if bucket_bytes <= ONESHOT_MAX_BYTES else ("nvls" if self.multicast_ptr else "twoshot")
+            algo = "oneshot" if bucket_bytes <= oneshot_max_bytes(self.world) else ("nvls" if self.multicast_ptr else "twoshot")
         if algo == "nvls" and not self.multicast_ptr:
             algo = "twoshot"
         st = self._by_algo.get(algo)

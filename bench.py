@@ -52,6 +52,8 @@ def _parse():
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--no-overlap", action="store_true")
     p.add_argument("--no-pump", action="store_true", help="e2e: drive every step from Python")
+    p.add_argument("--conv", choices=["auto", "simt", "tc"], default="auto",
+                   help="convolution kernels: CUDA-core fp32 or window-tile tcgen05 (auto: by model size)")
     p.add_argument("--input", choices=["u8", "f32"], default="u8", help="host->device input format (e2e)")
     p.add_argument("--dtype", choices=["auto", "fp32", "tf32"], default="auto",
                    help="tf32 = tcgen05 tensor-core GEMMs on fp32 tensors; fp32 = exact CUDA-core kernels")
@@ -112,7 +114,7 @@ def run_own(args):
     torch.manual_seed(5)
     stepper = NativeStepper(ctx, cfg, OptHyper(args.optimizer, lr=0.1 if args.optimizer == "adadelta" else 0.01),
                             batch=batch, loss_mode="ref", spec=spec, graph=not args.no_graph,
-                            overlap=not args.no_overlap, dtype=args.dtype)
+                            overlap=not args.no_overlap, dtype=args.dtype, conv=args.conv)
     K, W = args.steps, args.warmup
 
     # ---- device-resident input pool larger than L2, cycled (timing rule) ----

@@ -28,6 +28,7 @@ constexpr int RU_NT = 256;
 constexpr int RU_CHUNK = 1024;        // floats per CTA iteration (float4 per thread)
 constexpr int RU_MAX_CTAS = 148 * 2;  // = resident CTAs (2 per SM at this register count): one handshake wave,
                                       // larger buckets loop over chunks inside each CTA
+constexpr int RU_UNROLL = 4;          // chunks whose loads are issued together
 constexpr int RU_PSLICE = 32;         // floats per CTA when partial rows are pre-reduced
 constexpr int RU_FLAG_GRAIN = 32;     // one flag slot per 32 arena floats
 constexpr unsigned RU_SPIN_LIMIT = 1u << 28;
@@ -120,12 +121,21 @@ struct RUCtx {
     float* param; float* grad; float* state0; float* state1; uint16_t* shadow;
 };
 
-__device__ __forceinline__ void ru_update(const RUCtx& c, int idx, float4 g) {
-    float4 p = *reinterpret_cast<float4*>(c.param + idx);
-    float4 s0 = *reinterpret_cast<float4*>(c.state0 + idx);
-    float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f);
+// The update of one float4 is split into its loads and its math+stores so that a loop can put the loads of
+// several chunks in flight before the first dependent instruction (one chunk at a time is latency-bound:
+// 16 bytes per thread per memory round trip).
+struct RULoaded { float4 p, s0, s1; };
+__device__ __forceinline__ RULoaded ru_load(const RUCtx& c, int idx) {
+    RULoaded L;
+    L.p = *reinterpret_cast<const float4*>(c.param + idx);
+    L.s0 = *reinterpret_cast<const float4*>(c.state0 + idx);
+    L.s1 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c.kind != 1) L.s1 = *reinterpret_cast<const float4*>(c.state1 + idx);
+    return L;
+}
+__device__ __forceinline__ void ru_apply(const RUCtx& c, int idx, float4 g, RULoaded L) {
+    float4 p = L.p, s0 = L.s0, s1 = L.s1;
     const bool two = (c.kind != 1);
-    if (two) s1 = *reinterpret_cast<float4*>(c.state1 + idx);
     opt_apply(c.kind, c.h, g.x, p.x, s0.x, s1.x);
     opt_apply(c.kind, c.h, g.y, p.y, s0.y, s1.y);
     opt_apply(c.kind, c.h, g.z, p.z, s0.z, s1.z);
@@ -141,6 +151,7 @@ __device__ __forceinline__ void ru_update(const RUCtx& c, int idx, float4 g) {
         *reinterpret_cast<uint2*>(c.shadow + idx) = packed;
     }
 }
+__device__ __forceinline__ void ru_update(const RUCtx& c, int idx, float4 g) { ru_apply(c, idx, g, ru_load(c, idx)); }
 
 // spin until *flag >= gen (generation numbers only grow); bounded so a dead peer is an error, not a hang
 __device__ __forceinline__ bool ru_wait(const uint32_t* flag, uint32_t gen) {
@@ -210,8 +221,16 @@ __global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
     };
 
     if (world == 1) {
-        for (int c = 0; c < chunks; ++c)
-            if (active(c)) ru_update(cx, base_idx + c * RU_CHUNK, local_g(c));
+        for (int c0 = 0; c0 < chunks; c0 += RU_UNROLL) {
+            float4 g[RU_UNROLL];
+            RULoaded L[RU_UNROLL];
+#pragma unroll
+            for (int u = 0; u < RU_UNROLL; ++u)
+                if (c0 + u < chunks && active(c0 + u)) { g[u] = local_g(c0 + u); L[u] = ru_load(cx, base_idx + (c0 + u) * RU_CHUNK); }
+#pragma unroll
+            for (int u = 0; u < RU_UNROLL; ++u)
+                if (c0 + u < chunks && active(c0 + u)) ru_apply(cx, base_idx + (c0 + u) * RU_CHUNK, g[u], L[u]);
+        }
     } else {
         // ---- B: all-reduce over peer memory ----
         const int parity = gen & 1u;
@@ -288,11 +307,18 @@ __global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
                     if (tid == 0) atomicExch(a.step_counter + 2, 1u);
                     return;
                 }
-                for (int c = 0; c < chunks; ++c) {
-                    if (active(c)) {
-                        const float4 t = ld_volatile_f4(my_stage + landing + base_idx + c * RU_CHUNK);
-                        ru_update(cx, base_idx + c * RU_CHUNK, scale4(t, inv));
-                    }
+                for (int c0 = 0; c0 < chunks; c0 += RU_UNROLL) {
+                    float4 t[RU_UNROLL];
+                    RULoaded L[RU_UNROLL];
+#pragma unroll
+                    for (int u = 0; u < RU_UNROLL; ++u)
+                        if (c0 + u < chunks && active(c0 + u)) {
+                            t[u] = ld_volatile_f4(my_stage + landing + base_idx + (c0 + u) * RU_CHUNK);
+                            L[u] = ru_load(cx, base_idx + (c0 + u) * RU_CHUNK);
+                        }
+#pragma unroll
+                    for (int u = 0; u < RU_UNROLL; ++u)
+                        if (c0 + u < chunks && active(c0 + u)) ru_apply(cx, base_idx + (c0 + u) * RU_CHUNK, scale4(t[u], inv), L[u]);
                 }
             } else {
                 if (tid < world && tid != rank)
@@ -302,21 +328,38 @@ __global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
                     if (tid == 0) atomicExch(a.step_counter + 2, 1u);
                     return;
                 }
-                for (int c = 0; c < chunks; ++c) {
-                    if (active(c)) {
-                        const int idx = base_idx + c * RU_CHUNK;
-                        float4 s;
-                        if (a.comm.algo == 2) {
-                            s = multimem_ld_reduce_f4(a.comm.mc_stage + pbase + idx);       // in-switch sum of all ranks
-                            multimem_st_f4(a.comm.mc_stage + landing + idx, s);             // in-switch broadcast
-                        } else {
-                            s = sum_ranks(c);
+                if (a.comm.algo == 2) {
+                    // NVLS: the in-switch reductions of several chunks are in flight together
+                    for (int c0 = 0; c0 < chunks; c0 += RU_UNROLL) {
+                        float4 s[RU_UNROLL];
+                        RULoaded L[RU_UNROLL];
+#pragma unroll
+                        for (int u = 0; u < RU_UNROLL; ++u)
+                            if (c0 + u < chunks && active(c0 + u)) {
+                                const int idx = base_idx + (c0 + u) * RU_CHUNK;
+                                s[u] = multimem_ld_reduce_f4(a.comm.mc_stage + pbase + idx);   // in-switch sum of all ranks
+                                L[u] = ru_load(cx, idx);
+                            }
+#pragma unroll
+                        for (int u = 0; u < RU_UNROLL; ++u)
+                            if (c0 + u < chunks && active(c0 + u)) {
+                                const int idx = base_idx + (c0 + u) * RU_CHUNK;
+                                multimem_st_f4(a.comm.mc_stage + landing + idx, s[u]);         // in-switch broadcast
+                                ru_apply(cx, idx, scale4(s[u], inv), L[u]);
+                            }
+                    }
+                } else {
+                    for (int c = 0; c < chunks; ++c) {
+                        if (active(c)) {
+                            const int idx = base_idx + c * RU_CHUNK;
+                            const RULoaded L = ru_load(cx, idx);
+                            const float4 s = sum_ranks(c);
 #pragma unroll
                             for (int r = 0; r < 8; ++r)          // push the sum into every peer's landing area
                                 if (r < world && r != rank)
                                     *reinterpret_cast<float4*>(a.comm.stage[r] + landing + idx) = s;
+                            ru_apply(cx, idx, scale4(s, inv), L);
                         }
-                        ru_update(cx, idx, scale4(s, inv));
                     }
                 }
                 __threadfence_system();
