@@ -109,6 +109,7 @@ class NativeLeNet:
         self.conv_offsets = tuple(sl[k].offset - s0 for k in
                                   ("ConvNet.1.weight", "ConvNet.1.bias", "ConvNet.4.weight", "ConvNet.4.bias"))
         self.launches_per_step = 0
+        self.gemm_ws = native.GemmWorkspace(self.device) if self.tc else None
 
     def dims(self, b: int) -> native.Dims:
         c = self.cfg
@@ -133,9 +134,9 @@ class NativeLeNet:
         if self.tc:
             T = native.tc_problem
             native.tc_gemm_group([T(self.p2, self.ld_p2, False, w["ConvNet.7.weight"], k3, False, b, c.c3, k3,
-                                    bias=w["ConvNet.7.bias"], act=1, out=self.a3, ld_out=self.ld_a3)])
+                                    bias=w["ConvNet.7.bias"], act=1, out=self.a3, ld_out=self.ld_a3)], self.gemm_ws)
             native.tc_gemm_group([T(self.a3, self.ld_a3, False, w["FC.0.weight"], c.c3, False, b, c.f1, c.c3,
-                                    bias=w["FC.0.bias"], act=1, out=self.h1, ld_out=self.ld_h1)])
+                                    bias=w["FC.0.bias"], act=1, out=self.h1, ld_out=self.ld_h1)], self.gemm_ws)
         else:
             native.linear_fwd(self.p2[:b].view(b, -1), w["ConvNet.7.weight"].view(c.c3, -1),
                               w["ConvNet.7.bias"], self.a3[:b], 1)
@@ -162,7 +163,7 @@ class NativeLeNet:
                 # dz3 = (dz1 Wfc1) * leaky'(a3)
                 T(self.dz1, c.f1, False, w["FC.0.weight"], c.c3, True, b, c.c3, c.f1,
                   mask=self.a3, ld_mask=self.ld_a3, out=self.dz3, ld_out=c.c3),
-            ])
+            ], self.gemm_ws)
             if on_bucket:
                 on_bucket(0)
             native.tc_gemm_group([
@@ -171,7 +172,7 @@ class NativeLeNet:
                   out=g["ConvNet.7.weight"], ld_out=k3, colext=g["ConvNet.7.bias"]),
                 # dp2 = dz3 W3 (pool/activation masks are applied inside conv_bwd)
                 T(self.dz3, c.c3, False, w["ConvNet.7.weight"], k3, True, b, k3, c.c3, out=self.dp2, ld_out=k3),
-            ])
+            ], self.gemm_ws)
             if on_bucket:
                 on_bucket(1)
         else:
@@ -270,7 +271,8 @@ class NativeStepper:
                              net.partials if is_conv else None, net.cur_partials if is_conv else 0,
                              net.partial_stride if is_conv else 0, opt.hyper.code(), self.hyper_dev,
                              self.step_counter, bucket_index == 2,
-                             self.comm.struct_for(b.numel * 4) if (self.comm and not self._comm_off) else None,
+                             self.comm.struct_for(b.numel * 4, overlapped=self.overlap and bucket_index != 2)
+                             if (self.comm and not self._comm_off) else None,
                              net.loss, self.loss_sink)
 
     def _step_body(self, x: torch.Tensor, y: torch.Tensor) -> None:

@@ -41,7 +41,7 @@ class TcProblem(C.Structure):
 class Comm(C.Structure):
     _fields_ = [("world", C.c_int), ("rank", C.c_int), ("algo", C.c_int),
                 ("stage", C.c_void_p * 8), ("flags", C.c_void_p * 8), ("mc_stage", C.c_void_p),
-                ("arena_len", C.c_int), ("max_slices", C.c_int)]
+                ("arena_len", C.c_int), ("max_slices", C.c_int), ("max_ctas", C.c_int)]
 
 
 class PumpDesc(C.Structure):
@@ -78,6 +78,9 @@ def load(build_if_missing: bool = True):
     lib.b200dp_head_tail.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, vp]
     lib.b200dp_linear_bwd_group.argtypes = [C.POINTER(BwdProblem), i, vp]
     lib.b200dp_tc_gemm_group.argtypes = [C.POINTER(TcProblem), i, vp]
+    lib.b200dp_tc_gemm_group_splitk.argtypes = [C.POINTER(TcProblem), i, vp, C.c_long, vp, i, vp]
+    lib.b200dp_tc_gemm_ws_floats.argtypes = [C.POINTER(TcProblem), i, C.POINTER(C.c_int)]
+    lib.b200dp_tc_gemm_ws_floats.restype = C.c_long
     lib.b200dp_conv_bwd_num_partials.argtypes = [Dims]
     lib.b200dp_tcw_pack_floats.argtypes = [Dims]
     lib.b200dp_tcw_pack_floats.restype = C.c_long
@@ -219,9 +222,33 @@ def tc_problem(a, lda: int, a_mn: bool, b, ldb: int, b_mn: bool, M: int, N: int,
                      _p(out), ld_out, _p(colext))
 
 
-def tc_gemm_group(problems: Sequence[TcProblem]) -> None:
+class GemmWorkspace:
+    """Split-K scratch of the tensor-core GEMM launches of one stream: partial tiles + per-tile tickets.  Grows on
+    demand (outside CUDA-graph capture: run the launch sequence once eagerly first)."""
+
+    def __init__(self, device):
+        self.device = device
+        self.ws = torch.empty(0, dtype=torch.float32, device=device)
+        self.tickets = torch.zeros(0, dtype=torch.int32, device=device)
+
+    def reserve(self, floats: int, tickets: int) -> None:
+        if floats > self.ws.numel():
+            self.ws = torch.empty(floats, dtype=torch.float32, device=self.device)
+        if tickets > self.tickets.numel():
+            self.tickets = torch.zeros(tickets, dtype=torch.int32, device=self.device)
+
+
+def tc_gemm_group(problems: Sequence[TcProblem], workspace: Optional[GemmWorkspace] = None) -> None:
     arr = (TcProblem * len(problems))(*problems)
-    check(load().b200dp_tc_gemm_group(arr, len(problems), _stream()), "tc_gemm_group")
+    if workspace is None:
+        check(load().b200dp_tc_gemm_group(arr, len(problems), _stream()), "tc_gemm_group")
+        return
+    nt = C.c_int(0)
+    need = int(load().b200dp_tc_gemm_ws_floats(arr, len(problems), C.byref(nt)))
+    workspace.reserve(need, nt.value)
+    check(load().b200dp_tc_gemm_group_splitk(arr, len(problems), _p(workspace.ws) if need else None, workspace.ws.numel(),
+                                             _p(workspace.tickets) if nt.value else None, workspace.tickets.numel(),
+                                             _stream()), "tc_gemm_group_splitk")
 
 
 def conv_bwd_num_partials(dims: Dims) -> int:

@@ -113,23 +113,28 @@ class P2PComm:
         return True
 
     # -- per-bucket algorithm choice ---------------------------------------------------
-    def struct_for(self, bucket_bytes: int) -> "native.Comm":
-        """The ``b200dp_comm`` to pass for a bucket of this size (algorithm chosen per bucket)."""
+    OVERLAP_CTAS = 32      # CTAs of a reduce+update that runs while backward kernels still need the SMs
+
+    def struct_for(self, bucket_bytes: int, overlapped: bool = False) -> "native.Comm":
+        """The ``b200dp_comm`` to pass for a bucket of this size (algorithm chosen per bucket).  ``overlapped``:
+        the launch shares the GPU with the rest of backward, so it is kept to a few CTAs (``max_ctas``)."""
         algo = self.algo
         if algo == "auto":
             algo = "oneshot" if bucket_bytes <= oneshot_max_bytes(self.world) else ("nvls" if self.multicast_ptr else "twoshot")
         if algo == "nvls" and not self.multicast_ptr:
             algo = "twoshot"
-        st = self._by_algo.get(algo)
+        key = (algo, bool(overlapped))
+        st = self._by_algo.get(key)
         if st is None:
             st = native.Comm()
+            st.max_ctas = self.OVERLAP_CTAS if overlapped else 0
             st.world, st.rank, st.algo = self.world, self.rank, ALGO_CODES[algo]
             st.arena_len, st.max_slices = self.arena_len, self.max_slices
             for r in range(self.world):
                 st.stage[r] = self.struct.stage[r]
                 st.flags[r] = self.struct.flags[r]
             st.mc_stage = self.multicast_ptr or None
-            self._by_algo[algo] = st
+            self._by_algo[key] = st
         return st
 
     def close(self) -> None:

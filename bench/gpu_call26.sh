@@ -1,0 +1,16 @@
+#!/bin/bash
+mkdir -p gpurun_out
+N=$(nvidia-smi -L | wc -l)
+timeout 900 python -m pytest tests/test_multi_gpu.py -m gpu -x -q --tb=short -p no:cacheprovider > gpurun_out/pytest_multi_n$N.log 2>&1
+echo "pytest rc=$?" >> gpurun_out/pytest_multi_n$N.log
+tail -n 3 gpurun_out/pytest_multi_n$N.log | cut -c1-300
+for cfg in wide_cifar lenet_b256; do
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29634 bench.py --gpus $N --steps 500 --warmup 50 --config $cfg > gpurun_out/bench_${cfg}_n$N.log 2>&1
+echo "$cfg rc=$?" >> gpurun_out/bench_${cfg}_n$N.log
+python - <<PY
+import json
+for l in open("gpurun_out/bench_${cfg}_n$N.log"):
+    if l.startswith("{"):
+        d=json.loads(l); print("$cfg", round(d["value"]), round(d["ms_per_step"]*1e3,1), "us/step; exposed", d["exposed_comm_us_per_step"], "e2e", round(d["e2e"]["value"]), d["clocks"])
+PY
+done

@@ -8,8 +8,8 @@ from b200dp.ops import native
 lib = native.load()
 lib.b200dp_tc_gemm_group_timed.argtypes = [C.POINTER(native.TcProblem), C.c_int, C.c_void_p, C.c_void_p]
 dev = "cuda"
-for (M, N, K, amn, bmn) in [(256, 120, 400, False, False), (256, 84, 120, False, False), (120, 401, 256, True, True),
-                            (256, 400, 120, False, True)]:
+for (M, N, K, amn, bmn) in [(256, 120, 400, False, False), (256, 480, 1600, False, False), (256, 336, 480, False, False),
+                            (480, 1601, 256, True, True), (256, 1600, 480, False, True)]:
     a = torch.randn((K, M + 4) if amn else (M, K + 4), device=dev)
     b = torch.randn((K, (N + 3) // 4 * 4) if bmn else (N, K + 4), device=dev)
     out = torch.empty(M, N, device=dev)
@@ -23,6 +23,25 @@ for (M, N, K, amn, bmn) in [(256, 120, 400, False, False), (256, 84, 120, False,
         rc = lib.b200dp_tc_gemm_group_timed(arr, 1, dbg.data_ptr(), torch.cuda.current_stream().cuda_stream)
         e1.record()
         torch.cuda.synchronize()
+    ws = native.GemmWorkspace(torch.device(dev))
+    def split_call():
+        native.tc_gemm_group([prob], ws)
+    for _ in range(3):
+        split_call()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(10):
+        split_call()
+    e1.record()
+    torch.cuda.synchronize()
+    t_split = e0.elapsed_time(e1) * 100
+    e0.record()
+    for _ in range(10):
+        native.tc_gemm_group([prob])
+    e1.record()
+    torch.cuda.synchronize()
+    t_plain = e0.elapsed_time(e1) * 100
+    print(f"   back-to-back x10: plain {t_plain:.1f} us/launch, split-K {t_split:.1f} us/launch (ws floats {ws.ws.numel()})")
     t = dbg.tolist()
     t0 = t[0]
     print(f"M{M} N{N} K{K} amn={amn} bmn={bmn}: event {e0.elapsed_time(e1)*1e3:.1f} us | setup {t[1]-t0} acc_done {t[2]-t0} "

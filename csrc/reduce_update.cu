@@ -29,7 +29,7 @@ constexpr int RU_CHUNK = 1024;        // floats per CTA iteration (float4 per th
 constexpr int RU_MAX_CTAS = 148 * 2;  // = resident CTAs (2 per SM at this register count): one handshake wave,
                                       // larger buckets loop over chunks inside each CTA
 constexpr int RU_UNROLL = 4;          // chunks whose loads are issued together
-constexpr int RU_PSLICE = 32;         // floats per CTA when partial rows are pre-reduced
+constexpr int RU_PSLICE = 128;        // floats per CTA when partial rows are pre-reduced (32 float4 columns x 8 row groups)
 constexpr int RU_FLAG_GRAIN = 32;     // one flag slot per 32 arena floats
 constexpr unsigned RU_SPIN_LIMIT = 1u << 28;
 
@@ -164,7 +164,7 @@ __device__ __forceinline__ bool ru_wait(const uint32_t* flag, uint32_t gen) {
 }
 
 __global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
-    __shared__ float sRed[8][RU_PSLICE];
+    __shared__ __align__(16) float sRed[8][RU_PSLICE];
     __shared__ __align__(16) float sSlice[RU_PSLICE];
     __shared__ int sTimeout;
     const int tid = threadIdx.x;
@@ -190,27 +190,27 @@ __global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
     // ---- A: (optional) sum the partial-gradient rows of this 32-float slice, fixed order ----
     const bool from_rows = a.partials != nullptr;
     if (from_rows) {
-        const int o = tid & 31, pg = tid >> 5;            // thread (o, pg) sums rows pg, pg+8, ...; then 8 -> 1
-        float s = 0.f;
-        if (o < n_here) {
-            const float* src = a.partials + off + o;
+        const int o = tid & 31, pg = tid >> 5;            // thread (o, pg) sums float4 column o of rows pg, pg+8, ...; then 8 -> 1
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (o * 4 < n_here) {
+            const float* src = a.partials + off + o * 4;  // off and partial_stride are multiples of 4: 16-byte aligned
             int r = pg;
             for (; r + 56 < a.n_partials; r += 64) {      // 8 independent loads in flight, added in row order
-                float t[8];
+                float4 t[8];
 #pragma unroll
-                for (int u = 0; u < 8; ++u) t[u] = __ldcg(src + (long)(r + 8 * u) * a.partial_stride);
+                for (int u = 0; u < 8; ++u) t[u] = __ldcg(reinterpret_cast<const float4*>(src + (long)(r + 8 * u) * a.partial_stride));
 #pragma unroll
-                for (int u = 0; u < 8; ++u) s += t[u];
+                for (int u = 0; u < 8; ++u) s = add4(s, t[u]);
             }
-            for (; r < a.n_partials; r += 8) s += __ldcg(src + (long)r * a.partial_stride);
+            for (; r < a.n_partials; r += 8) s = add4(s, __ldcg(reinterpret_cast<const float4*>(src + (long)r * a.partial_stride)));
         }
-        sRed[pg][o] = s;
+        *reinterpret_cast<float4*>(&sRed[pg][o * 4]) = s;
         __syncthreads();
-        if (tid < RU_PSLICE) {
-            float t = 0.f;
+        if (tid < 32) {
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int q = 0; q < 8; ++q) t += sRed[q][tid];
-            sSlice[tid] = t;
+            for (int q = 0; q < 8; ++q) t = add4(t, *reinterpret_cast<const float4*>(&sRed[q][tid * 4]));
+            *reinterpret_cast<float4*>(sSlice + tid * 4) = t;
         }
         __syncthreads();
     }
@@ -408,6 +408,8 @@ extern "C" int b200dp_reduce_update(float* param, float* grad, float* state0, fl
                                     uint32_t* step_counter, int last_bucket, const b200dp_comm* comm,
                                     const float* loss_src, const uint64_t* loss_sink, b200dp_stream_t s) {
     B200DP_REQUIRE(start % 128 == 0 && count % 4 == 0 && count > 0, "bucket must be 128-aligned");
+    B200DP_REQUIRE(partials == nullptr || (partial_stride % 4 == 0 && ((uintptr_t)partials & 15) == 0),
+                   "partial rows must be 16-byte aligned with a row pitch that is a multiple of 4 floats");
     B200DP_REQUIRE(opt_kind >= 0 && opt_kind <= 2, "opt_kind 0 adadelta, 1 sgd, 2 adam");
     RUArgs a{};
     a.param = param; a.grad = grad; a.state0 = state0; a.state1 = state1; a.shadow = shadow_bf16;
@@ -427,7 +429,8 @@ extern "C" int b200dp_reduce_update(float* param, float* grad, float* state0, fl
     if (partials) {
         a.slice = RU_PSLICE;
     } else {
-        const int per_cta = (count + RU_MAX_CTAS - 1) / RU_MAX_CTAS;
+        const int cap = (comm && comm->max_ctas > 0 && comm->max_ctas < RU_MAX_CTAS) ? comm->max_ctas : RU_MAX_CTAS;
+        const int per_cta = (count + cap - 1) / cap;
         a.slice = (per_cta + RU_CHUNK - 1) / RU_CHUNK * RU_CHUNK;
         if (a.slice < RU_CHUNK) a.slice = RU_CHUNK;
     }

@@ -9,14 +9,18 @@
 // Replaces reference cnn.py:16-17, 20-21 (conv3-as-GEMM, FC.0) and their autograd backward
 // (train.py:49), up to four problems per launch.
 //
-// Structure (one CTA = one 128x128 output tile; 192 threads):
+// Structure (one CTA = one 128 x bn output tile, or one K-split of it; 320 threads):
 //   warp 0     TMA producer: cp.async.bulk.tensor.2d (SWIZZLE_128B, zero fill out of bounds) into a
 //              6-stage ring of {A 16 KB, B 16 KB} slabs, 32 k per slab, mbarrier complete_tx
 //   warp 1     allocates 128 TMEM columns, then one elected thread issues 4 tcgen05.mma
 //              (M128 N128 K8, tf32) per slab and tcgen05.commit's the slab's "empty" barrier
-//   warps 2-5  epilogue: tcgen05.ld 32x32b.x16 (thread = output row), bias / LeakyReLU /
-//              LeakyReLU' mask, fp32 stores; the last logical column can be routed to a separate
-//              vector (bias gradient through a ones column in the activation buffers)
+//   warps 2-9  epilogue: tcgen05.ld 32x32b.x16 (thread = output row, 64 contiguous bytes per load), bias /
+//              LeakyReLU / LeakyReLU' mask, stores straight from registers; the last logical column can be
+//              routed to a separate vector (bias gradient through a ones column in the activation buffers)
+// With a workspace the launch is re-tiled (32/64/128-wide tiles) and split along K so that about one CTA per
+// SM works: a CTA is bound by the rate at which TMA delivers 128-byte rows (~43 B/clk, measured 765 cycles per
+// 32 KB slab), so a 50-slab chain on 8 CTAs costs 20 us while 120 CTAs with 12 slabs each cost ~3 us; the CTAs
+// of a tile park raw partials and the last one (ticket) sums them in split order: deterministic.
 #include <cuda.h>
 #include <string.h>
 
@@ -25,13 +29,14 @@
 
 namespace b200dp {
 
-constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 32;
+constexpr int TC_BM = 128, TC_BN_MAX = 128, TC_BK = 32;
 constexpr int TC_STAGES = 6;
-constexpr int TC_A_BYTES = TC_BM * TC_BK * 4;   // 16 KB
-constexpr int TC_B_BYTES = TC_BN * TC_BK * 4;   // 16 KB
+constexpr int TC_A_BYTES = TC_BM * TC_BK * 4;       // 16 KB
+constexpr int TC_B_BYTES = TC_BN_MAX * TC_BK * 4;   // up to 16 KB (bn * 128 B are used)
 constexpr int TC_STAGE_BYTES = TC_A_BYTES + TC_B_BYTES;
 constexpr int TC_SMEM = TC_STAGES * TC_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
-constexpr int TC_THREADS = 192;
+constexpr int TC_EPI_WARPS = 8;
+constexpr int TC_THREADS = 32 * (2 + TC_EPI_WARPS);
 constexpr int TC_TMEM_COLS = 128;
 constexpr int TC_MAX_PROBLEMS = 4;
 
@@ -43,7 +48,11 @@ struct TcProblem {
     float* colext;           // if set: logical column N-1 goes to colext[m] (not to out)
     int M, N, K;
     int a_mn, b_mn, act;
-    int tiles_n, tile_start;
+    int bn;                  // tile width (32 / 64 / 128)
+    int splits;              // split-K factor: CTAs per output tile
+    int tiles_n, cta_start;  // first CTA of this problem
+    float* ws;               // split-K partial tiles [tile][split][128][bn]
+    unsigned* tickets;       // one arrival counter per tile (zero between launches)
 };
 struct TcGroup {
     TcProblem p[TC_MAX_PROBLEMS];
@@ -70,8 +79,8 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, int mn_major) {
 // constant addresses and keeps the values in registers.
 struct TcScalars {
     const CUtensorMap* tmA; const CUtensorMap* tmB;
-    const float* bias; const float* mask; float* out; float* colext;
-    int ld_mask, ld_out, M, N, K, a_mn, b_mn, act, tiles_n, tile_start;
+    const float* bias; const float* mask; float* out; float* colext; float* ws; unsigned* tickets;
+    int ld_mask, ld_out, M, N, K, a_mn, b_mn, act, bn, splits, tiles_n, cta_start;
 };
 __device__ __forceinline__ TcScalars tc_load_scalars(const TcGroup& g, int pi) {
     TcScalars r;
@@ -79,7 +88,8 @@ __device__ __forceinline__ TcScalars tc_load_scalars(const TcGroup& g, int pi) {
     case i: r.tmA = &g.p[i].tmA; r.tmB = &g.p[i].tmB; r.bias = g.p[i].bias; r.mask = g.p[i].mask;          \
             r.out = g.p[i].out; r.colext = g.p[i].colext; r.ld_mask = g.p[i].ld_mask; r.ld_out = g.p[i].ld_out; \
             r.M = g.p[i].M; r.N = g.p[i].N; r.K = g.p[i].K; r.a_mn = g.p[i].a_mn; r.b_mn = g.p[i].b_mn;      \
-            r.act = g.p[i].act; r.tiles_n = g.p[i].tiles_n; r.tile_start = g.p[i].tile_start; break;
+            r.act = g.p[i].act; r.bn = g.p[i].bn; r.splits = g.p[i].splits; r.tiles_n = g.p[i].tiles_n;     \
+            r.cta_start = g.p[i].cta_start; r.ws = g.p[i].ws; r.tickets = g.p[i].tickets; break;
     switch (pi) {
         TC_COPY(1) TC_COPY(2) TC_COPY(3)
         default: TC_COPY(0)
@@ -97,18 +107,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     const uint32_t tmem_full_bar = bar_base + 8u * (2 * TC_STAGES);
     const uint32_t tmem_slot = bar_base + 8u * (2 * TC_STAGES + 1);
     uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+    int* s_last = reinterpret_cast<int*>(tmem_slot_ptr + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) TC_STAMP(0);
     int pi = 0;
-    if (g.count > 1 && (int)blockIdx.x >= g.p[1].tile_start) pi = 1;
-    if (g.count > 2 && (int)blockIdx.x >= g.p[2].tile_start) pi = 2;
-    if (g.count > 3 && (int)blockIdx.x >= g.p[3].tile_start) pi = 3;
+    if (g.count > 1 && (int)blockIdx.x >= g.p[1].cta_start) pi = 1;
+    if (g.count > 2 && (int)blockIdx.x >= g.p[2].cta_start) pi = 2;
+    if (g.count > 3 && (int)blockIdx.x >= g.p[3].cta_start) pi = 3;
     const TcScalars P = tc_load_scalars(g, pi);
-    const int tile = blockIdx.x - P.tile_start;
+    const int local = blockIdx.x - P.cta_start;
+    const int tile = local / P.splits, split = local - tile * P.splits;
     const int tm = tile / P.tiles_n, tn = tile - tm * P.tiles_n;
-    const int m0 = tm * TC_BM, n0 = tn * TC_BN;
-    const int nslab = (P.K + TC_BK - 1) / TC_BK;
+    const int m0 = tm * TC_BM, n0 = tn * P.bn;
+    // this CTA's K range: slabs [slab0, slab0 + nslab)
+    const int nslab_all = (P.K + TC_BK - 1) / TC_BK;
+    const int per = nslab_all / P.splits, rem = nslab_all - per * P.splits;
+    const int nslab = per + (split < rem ? 1 : 0);
+    const int slab0 = split * per + min(split, rem);
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < TC_STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
@@ -125,12 +141,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     if (warp == 0) {
         // ================= TMA producer =================
         if (lane == 0) {
+            const uint32_t stage_tx = TC_A_BYTES + (uint32_t)P.bn * 128u;
             for (int s = 0; s < nslab; ++s) {
                 const int st = s % TC_STAGES;
                 if (s >= TC_STAGES) mbar_wait(empty_bar(st), ((s / TC_STAGES) - 1) & 1);
                 const uint32_t sa = base + st * TC_STAGE_BYTES, sb = sa + TC_A_BYTES;
-                mbar_expect_tx(full_bar(st), TC_STAGE_BYTES);
-                const int k0 = s * TC_BK;
+                mbar_expect_tx(full_bar(st), stage_tx);
+                const int k0 = (slab0 + s) * TC_BK;
                 if (P.a_mn) {
 #pragma unroll
                     for (int i = 0; i < TC_BM / 32; ++i) tma_load_2d(sa + i * (TC_BK * 128), P.tmA, full_bar(st), m0 + 32 * i, k0);
@@ -138,8 +155,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
                     tma_load_2d(sa, P.tmA, full_bar(st), k0, m0);
                 }
                 if (P.b_mn) {
-#pragma unroll
-                    for (int i = 0; i < TC_BN / 32; ++i) tma_load_2d(sb + i * (TC_BK * 128), P.tmB, full_bar(st), n0 + 32 * i, k0);
+                    for (int i = 0; i < P.bn / 32; ++i) tma_load_2d(sb + i * (TC_BK * 128), P.tmB, full_bar(st), n0 + 32 * i, k0);
                 } else {
                     tma_load_2d(sb, P.tmB, full_bar(st), k0, n0);
                 }
@@ -148,9 +164,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         }
     } else if (warp == 1) {
         // ================= MMA issuer =================
-        // instruction descriptor: D=f32, A=B=tf32, majorness per operand, N=128, M=128
+        // instruction descriptor: D=f32, A=B=tf32, majorness per operand, N=bn, M=128
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)P.a_mn << 15) | ((uint32_t)P.b_mn << 16) |
-                               ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+                               ((uint32_t)(P.bn >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
         const uint32_t a_step = P.a_mn ? 1024u : 32u;     // bytes per 8-k step inside a slab
         const uint32_t b_step = P.b_mn ? 1024u : 32u;
         for (int s = 0; s < nslab; ++s) {
@@ -171,49 +187,98 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
             __syncwarp();
         }
     } else {
-        // ================= epilogue (warps 2..5) =================
+        // ================= epilogue (warps 2..9): warp reads TMEM lane quarter warp%4, column half (warp-2)/4.
+        // thread = output row; it holds 16 consecutive columns per tcgen05.ld, i.e. 64 contiguous bytes of its row
+        // (two full 32-byte sectors), so results are stored straight from registers: no shared-memory transpose,
+        // no serial row loop (a lone warp per scheduler pays ~5 cycles per dependent instruction). =================
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
         if (threadIdx.x == 64) TC_STAMP(2);          // accumulator complete
-        const int q = warp & 3;                           // TMEM lane quarter this warp may touch
+        const int q = warp & 3;
+        const int h = (warp - 2) >> 2;
+        const int half = P.bn >> 1, c_lo = h * half;          // this warp's columns [c_lo, c_lo + half) of the tile
         const int n_out = P.colext ? P.N - 1 : P.N;
-        // Stage the warp's 32x128 fp32 sub-tile through shared memory (the operand ring is idle now)
-        // so that global stores are row-contiguous: lane = column.  Row pitch 129 floats: both the
-        // row-wise writes (lane = row) and the column-wise reads (lane = column) are conflict-free.
-        constexpr int TP = TC_BN + 1;
-        float* sT = reinterpret_cast<float*>(smem_raw + (base - smem_u32(smem_raw))) + q * 32 * TP;
-        const int ncols = min(TC_BN, P.N - n0);           // warp-uniform
-#pragma unroll 1
-        for (int c = 0; c * 16 < ncols; ++c) {
-            uint32_t r[16];
-            tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 16), r);
+        const int ncols = max(0, min(half, P.N - n0 - c_lo));  // warp-uniform
+        const int m = m0 + q * 32 + lane;
+        const bool row_ok = m < P.M;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c_lo;
+
+        auto finish16 = [&](int c, const float (&v)[16]) {     // fused epilogue of 16 columns of this thread's row
+            const int nb = n0 + c_lo + c * 16;
+            float bias_r[16], mask_r[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) sT[lane * TP + c * 16 + j] = __uint_as_float(r[j]);
-        }
-        __syncwarp();
-        float bias_r[TC_BN / 32];
+            for (int j = 0; j < 16; ++j) {
+                const bool ok = c * 16 + j < ncols && nb + j < n_out;
+                bias_r[j] = (P.bias && ok) ? __ldg(P.bias + nb + j) : 0.f;
+                mask_r[j] = (P.mask && ok && row_ok) ? P.mask[(long)m * P.ld_mask + nb + j] : 1.f;
+            }
+            if (!row_ok) return;
 #pragma unroll
-        for (int cc = 0; cc < TC_BN / 32; ++cc) {
-            const int n = n0 + cc * 32 + lane;
-            bias_r[cc] = (P.bias && n < n_out) ? P.bias[n] : 0.f;
-        }
-        const int rows = min(32, P.M - (m0 + q * 32));    // warp-uniform, may be <= 0
-#pragma unroll 1
-        for (int rr = 0; rr < rows; ++rr) {
-            const int m = m0 + q * 32 + rr;
-#pragma unroll
-            for (int cc = 0; cc < TC_BN / 32; ++cc) {
-                const int n = n0 + cc * 32 + lane;
-                if (cc * 32 < ncols && n < P.N) {
-                    float v = sT[rr * TP + cc * 32 + lane];
+            for (int j = 0; j < 16; ++j) {
+                if (c * 16 + j < ncols) {
+                    const int n = nb + j;
+                    float x = v[j];
                     if (n < n_out) {
-                        v += bias_r[cc];
-                        if (P.act == 1) v = leaky(v);
-                        if (P.mask) v *= leaky_grad_from_act(P.mask[(long)m * P.ld_mask + n]);
-                        P.out[(long)m * P.ld_out + n] = v;
+                        x += bias_r[j];
+                        if (P.act == 1) x = leaky(x);
+                        if (P.mask) x *= leaky_grad_from_act(mask_r[j]);
+                        P.out[(long)m * P.ld_out + n] = x;
                     } else {
-                        P.colext[m] = v;
+                        P.colext[m] = x;
                     }
+                }
+            }
+        };
+
+        if (P.splits == 1) {
+#pragma unroll 1
+            for (int c = 0; c * 16 < ncols; ++c) {
+                uint32_t r[16];
+                tmem_ld16(taddr + (uint32_t)(c * 16), r);
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+                finish16(c, v);
+            }
+        } else {
+            // ---- split-K: park the raw partial tile ([128][bn], 16-byte stores), take a ticket; the last CTA of the
+            //      tile sums the partials in split order (deterministic) and runs the epilogue ----
+            float* wt = P.ws + ((long)tile * P.splits + split) * (TC_BM * P.bn) + (q * 32 + lane) * P.bn + c_lo;
+#pragma unroll 1
+            for (int c = 0; c * 16 < ncols; ++c) {
+                uint32_t r[16];
+                tmem_ld16(taddr + (uint32_t)(c * 16), r);
+#pragma unroll
+                for (int j = 0; j < 16; j += 4)
+                    *reinterpret_cast<uint4*>(wt + c * 16 + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+            }
+            __threadfence();
+            asm volatile("bar.sync 2, %0;" ::"n"(32 * TC_EPI_WARPS) : "memory");
+            if (threadIdx.x == 64) {
+                const unsigned t = atomicAdd(P.tickets + tile, 1u);
+                const int last = (t == (unsigned)P.splits - 1u);
+                if (last) P.tickets[tile] = 0u;               // ready for the next launch / graph replay
+                *s_last = last;
+            }
+            asm volatile("bar.sync 2, %0;" ::"n"(32 * TC_EPI_WARPS) : "memory");
+            if (*s_last) {
+                __threadfence();
+                const float* w0 = P.ws + (long)tile * P.splits * (TC_BM * P.bn) + (q * 32 + lane) * P.bn + c_lo;
+                const long sstride = (long)TC_BM * P.bn;
+#pragma unroll 1
+                for (int c = 0; c * 16 < ncols; ++c) {
+                    float v[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] = 0.f;
+                    for (int sp = 0; sp < P.splits; ++sp) {
+                        const float4* src = reinterpret_cast<const float4*>(w0 + sp * sstride + c * 16);
+                        const float4 x0 = __ldcg(src), x1 = __ldcg(src + 1), x2 = __ldcg(src + 2), x3 = __ldcg(src + 3);
+                        v[0] += x0.x; v[1] += x0.y; v[2] += x0.z; v[3] += x0.w;
+                        v[4] += x1.x; v[5] += x1.y; v[6] += x1.z; v[7] += x1.w;
+                        v[8] += x2.x; v[9] += x2.y; v[10] += x2.z; v[11] += x2.w;
+                        v[12] += x3.x; v[13] += x3.y; v[14] += x3.z; v[15] += x3.w;
+                    }
+                    finish16(c, v);
                 }
             }
         }
@@ -269,20 +334,73 @@ static int encode_map(CUtensorMap* tm, const float* ptr, int rows, int cols, int
 
 using namespace b200dp;
 
-static int tc_launch(const b200dp_tc_problem* probs, int count, long long* dbg, b200dp_stream_t s);
+// Tiling plan of a group: tile width and split-K factor per problem, chosen so that the launch has about
+// one CTA per SM (these GEMMs are a few hundred MFLOP: a 128x128 tile per CTA leaves most of the GPU idle
+// behind a 50-slab dependency chain).  Without a workspace every problem runs unsplit on 128-wide tiles.
+struct TcPlan { int bn[TC_MAX_PROBLEMS], splits[TC_MAX_PROBLEMS], tiles[TC_MAX_PROBLEMS]; long ws_off[TC_MAX_PROBLEMS]; int tk_off[TC_MAX_PROBLEMS]; long ws_floats; int n_tickets; int ctas; };
+static void tc_plan(const b200dp_tc_problem* probs, int count, bool can_split, TcPlan& pl) {
+    const int target = 148;
+    auto tiles_for = [&](int bn) {
+        int t = 0;
+        for (int i = 0; i < count; ++i) t += ((probs[i].M + TC_BM - 1) / TC_BM) * ((probs[i].N + bn - 1) / bn);
+        return t;
+    };
+    int bn = 128;
+    if (can_split) {
+        if (tiles_for(128) < 48) bn = 64;
+        if (bn == 64 && tiles_for(64) < 48) bn = 32;
+    }
+    const int total_tiles = tiles_for(bn);
+    pl.ws_floats = 0; pl.n_tickets = 0; pl.ctas = 0;
+    for (int i = 0; i < count; ++i) {
+        const int nslab = (probs[i].K + TC_BK - 1) / TC_BK;
+        int sp = 1;
+        if (can_split && total_tiles < target) {
+            sp = target / total_tiles;
+            const int max_sp = nslab / 3 > 0 ? nslab / 3 : 1;          // at least 3 slabs per split
+            if (sp > max_sp) sp = max_sp;
+            if (sp > 16) sp = 16;
+            if (sp < 1) sp = 1;
+        }
+        pl.bn[i] = bn; pl.splits[i] = sp;
+        pl.tiles[i] = ((probs[i].M + TC_BM - 1) / TC_BM) * ((probs[i].N + bn - 1) / bn);
+        pl.ws_off[i] = pl.ws_floats; pl.tk_off[i] = pl.n_tickets;
+        if (sp > 1) { pl.ws_floats += (long)pl.tiles[i] * sp * TC_BM * bn; pl.n_tickets += pl.tiles[i]; }
+        pl.ctas += pl.tiles[i] * sp;
+    }
+}
+
+static int tc_launch(const b200dp_tc_problem* probs, int count, float* ws, long ws_floats, unsigned* tickets, int n_tickets,
+                     long long* dbg, b200dp_stream_t s);
 
 extern "C" int b200dp_tc_gemm_group(const b200dp_tc_problem* probs, int count, b200dp_stream_t s) {
-    return tc_launch(probs, count, nullptr, s);
+    return tc_launch(probs, count, nullptr, 0, nullptr, 0, nullptr, s);
+}
+extern "C" int b200dp_tc_gemm_group_splitk(const b200dp_tc_problem* probs, int count, float* ws, long ws_floats,
+                                           uint32_t* tickets, int n_tickets, b200dp_stream_t s) {
+    return tc_launch(probs, count, ws, ws_floats, tickets, n_tickets, nullptr, s);
+}
+extern "C" long b200dp_tc_gemm_ws_floats(const b200dp_tc_problem* probs, int count, int* n_tickets) {
+    if (count < 1 || count > TC_MAX_PROBLEMS) return -1;
+    TcPlan pl;
+    tc_plan(probs, count, true, pl);
+    if (n_tickets) *n_tickets = pl.n_tickets;
+    return pl.ws_floats;
 }
 // Profiling aid: same launch, CTA 0 writes clock64() stamps into dbg[0..32) (device memory):
 // [0] start, [1] setup done, [2] accumulator complete, [3] epilogue done, [4] end,
 // [8+s] producer issued slab s, [16+s] slab s landed (s < 8).
 extern "C" int b200dp_tc_gemm_group_timed(const b200dp_tc_problem* probs, int count, long long* dbg, b200dp_stream_t s) {
-    return tc_launch(probs, count, dbg, s);
+    return tc_launch(probs, count, nullptr, 0, nullptr, 0, dbg, s);
 }
 
-static int tc_launch(const b200dp_tc_problem* probs, int count, long long* dbg, b200dp_stream_t s) {
+static int tc_launch(const b200dp_tc_problem* probs, int count, float* ws, long ws_floats, unsigned* tickets, int n_tickets,
+                     long long* dbg, b200dp_stream_t s) {
     B200DP_REQUIRE(count >= 1 && count <= TC_MAX_PROBLEMS, "1..4 problems per launch");
+    TcPlan pl;
+    tc_plan(probs, count, ws != nullptr && tickets != nullptr, pl);
+    B200DP_REQUIRE(pl.ws_floats <= ws_floats && pl.n_tickets <= n_tickets,
+                   "split-K workspace too small: size it with b200dp_tc_gemm_ws_floats");
     TcGroup g;
     memset(&g, 0, sizeof(g));
     g.count = count;
@@ -292,20 +410,24 @@ static int tc_launch(const b200dp_tc_problem* probs, int count, long long* dbg, 
         const b200dp_tc_problem& q = probs[i];
         TcProblem& p = g.p[i];
         B200DP_REQUIRE(q.M > 0 && q.N > 0 && q.K > 0, "empty problem");
+        const int bn = pl.bn[i];
         int rc;
-        // K-major: memory [MN][K] -> box {32 k, 128 mn};  MN-major: memory [K][MN] -> box {32 mn, 32 k}
+        // K-major: memory [MN][K] -> box {32 k, rows mn};  MN-major: memory [K][MN] -> box {32 mn, 32 k}
         rc = q.a_mn_major ? encode_map(&p.tmA, q.a, q.K, q.M, q.lda, 32, TC_BK, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)
                           : encode_map(&p.tmA, q.a, q.M, q.K, q.lda, TC_BK, TC_BM, CU_TENSOR_MAP_SWIZZLE_128B);
         if (rc) return rc;
         rc = q.b_mn_major ? encode_map(&p.tmB, q.b, q.K, q.N, q.ldb, 32, TC_BK, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)
-                          : encode_map(&p.tmB, q.b, q.N, q.K, q.ldb, TC_BK, TC_BN, CU_TENSOR_MAP_SWIZZLE_128B);
+                          : encode_map(&p.tmB, q.b, q.N, q.K, q.ldb, TC_BK, bn, CU_TENSOR_MAP_SWIZZLE_128B);
         if (rc) return rc;
         p.bias = q.bias; p.mask = q.mask; p.ld_mask = q.ld_mask; p.out = q.out; p.ld_out = q.ld_out;
         p.colext = q.colext; p.M = q.M; p.N = q.N; p.K = q.K;
         p.a_mn = q.a_mn_major ? 1 : 0; p.b_mn = q.b_mn_major ? 1 : 0; p.act = q.act;
-        p.tiles_n = (q.N + TC_BN - 1) / TC_BN;
-        p.tile_start = total;
-        total += ((q.M + TC_BM - 1) / TC_BM) * p.tiles_n;
+        p.bn = bn; p.splits = pl.splits[i];
+        p.tiles_n = (q.N + bn - 1) / bn;
+        p.cta_start = total;
+        p.ws = ws ? ws + pl.ws_off[i] : nullptr;
+        p.tickets = tickets ? tickets + pl.tk_off[i] : nullptr;
+        total += pl.tiles[i] * pl.splits[i];
     }
     static bool attr_done = false;
     if (!attr_done) {

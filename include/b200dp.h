@@ -104,6 +104,14 @@ typedef struct {
     float* colext;
 } b200dp_tc_problem;
 int b200dp_tc_gemm_group(const b200dp_tc_problem* probs, int count, b200dp_stream_t s);
+/* Same, with a workspace: the launch is re-tiled (32/64/128-wide tiles) and split along K so that about one CTA per
+ * SM works on it; the CTAs of a tile park raw partial tiles in `ws`, and the last one to arrive (a ticket per tile in
+ * `tickets`, zero-initialised, left zero again) sums them in split order — deterministic — and runs the epilogue.
+ * Sizes from b200dp_tc_gemm_ws_floats (returns floats needed, *n_tickets = counters needed).  One launch at a time
+ * per workspace. */
+int b200dp_tc_gemm_group_splitk(const b200dp_tc_problem* probs, int count, float* ws, long ws_floats,
+                                uint32_t* tickets, int n_tickets, b200dp_stream_t s);
+long b200dp_tc_gemm_ws_floats(const b200dp_tc_problem* probs, int count, int* n_tickets);
 /* Profiling aid: same launch; CTA 0 records clock64() stamps of its pipeline phases in dbg[0..32). */
 int b200dp_tc_gemm_group_timed(const b200dp_tc_problem* probs, int count, long long* dbg, b200dp_stream_t s);
 
@@ -215,6 +223,10 @@ typedef struct {
     float* mc_stage;          /* multicast alias of the staging block (NVLS) or NULL */
     int arena_len;            /* floats per parity buffer */
     int max_slices;           /* flag slots per source rank (arena_len / 32) */
+    int max_ctas;             /* 0 = fill the GPU (2 CTAs per SM).  A bucket that is reduced WHILE backward kernels still
+                                 run should use few CTAs (32): CTAs that spin on a slow peer's flags would otherwise hold
+                                 the SMs the backward kernels need, and with several chunks in flight per thread a few
+                                 CTAs already cover the NVLink latency-bandwidth product */
 } b200dp_comm;
 
 int b200dp_reduce_update(float* param, float* grad, float* state0, float* state1, uint16_t* shadow_bf16,

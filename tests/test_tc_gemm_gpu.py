@@ -5,7 +5,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def _run(M, N, K, a_mn, b_mn, *, bias=False, act=0, mask=False, colext=False, pad=0):
+def _run(M, N, K, a_mn, b_mn, *, bias=False, act=0, mask=False, colext=False, pad=0, splitk=False):
     from b200dp.ops import native
     native.load()
     dev = "cuda"
@@ -25,9 +25,13 @@ def _run(M, N, K, a_mn, b_mn, *, bias=False, act=0, mask=False, colext=False, pa
     n_out = N - 1 if colext else N
     out = torch.full((M, n_out + 3), -5.0, device=dev)
     col = torch.full((M,), -5.0, device=dev) if colext else None
-    native.tc_gemm_group([native.tc_problem(a_buf, lda, a_mn, b_buf, ldb, b_mn, M, N, K, bias=bias_t, act=act,
-                                            mask=mask_t, ld_mask=N, out=out, ld_out=n_out + 3, colext=col)])
+    ws = native.GemmWorkspace(torch.device(dev)) if splitk else None
+    for _ in range(2 if splitk else 1):                  # twice: the tickets must come back to zero
+        native.tc_gemm_group([native.tc_problem(a_buf, lda, a_mn, b_buf, ldb, b_mn, M, N, K, bias=bias_t, act=act,
+                                                mask=mask_t, ld_mask=N, out=out, ld_out=n_out + 3, colext=col)], ws)
     torch.cuda.synchronize()
+    if splitk:
+        assert int(ws.tickets.abs().sum()) == 0
     ref = A.double() @ Bm.double().t()
     full = ref.clone()
     if bias:
@@ -49,7 +53,34 @@ def test_tc_gemm_majorness(a_mn, b_mn, M, N, K):
     _run(M, N, K, a_mn, b_mn)
 
 
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("M,N,K", [(256, 480, 1600), (256, 120, 400), (120, 401, 256), (37, 84, 120), (480, 1601, 256)])
+def test_tc_gemm_splitk(a_mn, b_mn, M, N, K):
+    """Re-tiled + split-K launch (workspace given): same results, deterministic, tickets reset."""
+    _run(M, N, K, a_mn, b_mn, splitk=True, bias=True, act=1)
+
+
+def test_tc_gemm_splitk_deterministic():
+    from b200dp.ops import native
+    native.load()
+    dev = torch.device("cuda")
+    torch.manual_seed(3)
+    A, Bm = torch.randn(256, 1600, device=dev), torch.randn(480, 1600, device=dev)
+    ws = native.GemmWorkspace(dev)
+    outs = []
+    for _ in range(3):
+        out = torch.empty(256, 480, device=dev)
+        native.tc_gemm_group([native.tc_problem(A, 1600, False, Bm, 1600, False, 256, 480, 1600, out=out, ld_out=480)], ws)
+        torch.cuda.synchronize()
+        outs.append(out)
+    assert ws.ws.numel() > 0                              # this shape does get split
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
 def test_tc_gemm_epilogues():
+    _run(256, 480, 1600, False, False, bias=True, act=1, pad=4, splitk=True)
+    _run(120, 401, 256, True, True, colext=True, splitk=True)
+    _run(256, 120, 84, False, True, mask=True, splitk=True)
     _run(256, 120, 400, False, False, bias=True, act=1)
     _run(256, 120, 84, False, True, mask=True)
     _run(120, 401, 256, True, True, colext=True)
