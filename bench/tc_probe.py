@@ -45,4 +45,4 @@ for (M, N, K, amn, bmn) in [(256, 120, 400, False, False), (256, 480, 1600, Fals
     t = dbg.tolist()
     t0 = t[0]
     print(f"M{M} N{N} K{K} amn={amn} bmn={bmn}: event {e0.elapsed_time(e1)*1e3:.1f} us | setup {t[1]-t0} acc_done {t[2]-t0} "
-          f"epi_done {t[3]-t0} end {t[4]-t0} | issued {[x-t0 for x in t[8:16] if x]} | landed {[x-t0 for x in t[16:24] if x]}")
+          f"staged {t[5]-t0} epi_done {t[3]-t0} end {t[4]-t0} | issued {[x-t0 for x in t[8:16] if x]} | landed {[x-t0 for x in t[16:24] if x]}")

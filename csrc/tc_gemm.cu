@@ -188,9 +188,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         }
     } else {
         // ================= epilogue (warps 2..9): warp reads TMEM lane quarter warp%4, column half (warp-2)/4.
-        // thread = output row; it holds 16 consecutive columns per tcgen05.ld, i.e. 64 contiguous bytes of its row
-        // (two full 32-byte sectors), so results are stored straight from registers: no shared-memory transpose,
-        // no serial row loop (a lone warp per scheduler pays ~5 cycles per dependent instruction). =================
+        // tcgen05.ld gives a thread 16 columns of ITS row; storing those directly costs one L1 wavefront per
+        // element (32 lanes -> 32 different lines; measured: 16 K cycles for a 128x128 tile, the whole epilogue).
+        // So the warp's 32 x half sub-tile is transposed through shared memory (the operand ring is idle now) and
+        // written with lane = column: one 128-byte wavefront per row.  The row loop is unrolled so the loads of
+        // several rows are in flight (a lone warp per scheduler pays the full latency of every dependent step). =====
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
         if (threadIdx.x == 64) TC_STAMP(2);          // accumulator complete
@@ -198,59 +200,66 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         const int h = (warp - 2) >> 2;
         const int half = P.bn >> 1, c_lo = h * half;          // this warp's columns [c_lo, c_lo + half) of the tile
         const int n_out = P.colext ? P.N - 1 : P.N;
+        constexpr int TP = TC_BN_MAX / 2 + 1;                  // odd pitch: row-wise writes and column-wise reads conflict-free
+        float* sT = reinterpret_cast<float*>(smem_raw + (base - smem_u32(smem_raw))) + (warp - 2) * 32 * TP;
         const int ncols = max(0, min(half, P.N - n0 - c_lo));  // warp-uniform
-        const int m = m0 + q * 32 + lane;
-        const bool row_ok = m < P.M;
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c_lo;
-
-        auto finish16 = [&](int c, const float (&v)[16]) {     // fused epilogue of 16 columns of this thread's row
-            const int nb = n0 + c_lo + c * 16;
-            float bias_r[16], mask_r[16];
+#pragma unroll 1
+        for (int c = 0; c * 16 < ncols; ++c) {
+            uint32_t r[16];
+            tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c_lo + c * 16), r);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const bool ok = c * 16 + j < ncols && nb + j < n_out;
-                bias_r[j] = (P.bias && ok) ? __ldg(P.bias + nb + j) : 0.f;
-                mask_r[j] = (P.mask && ok && row_ok) ? P.mask[(long)m * P.ld_mask + nb + j] : 1.f;
+            for (int j = 0; j < 16; ++j) sT[lane * TP + c * 16 + j] = __uint_as_float(r[j]);
+        }
+        __syncwarp();
+        if (threadIdx.x == 64) TC_STAMP(5);
+        const int rows = max(0, min(32, P.M - (m0 + q * 32)));    // warp-uniform
+        const int nchunk = (ncols + 31) >> 5;                      // 0..2 column chunks of 32 (lane = column)
+        const int mrow0 = m0 + q * 32, ncol0 = n0 + c_lo + lane;
+        float bias_r[2];
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            const int n = ncol0 + cc * 32;
+            bias_r[cc] = (P.bias && cc < nchunk && cc * 32 + lane < ncols && n < n_out) ? __ldg(P.bias + n) : 0.f;
+        }
+        auto finish = [&](int rr, int cc, float v) {      // fused epilogue of one element (lane = column)
+            const int m = mrow0 + rr, n = ncol0 + cc * 32;
+            if (n < n_out) {
+                v += cc == 0 ? bias_r[0] : bias_r[1];
+                if (P.act == 1) v = leaky(v);
+                if (P.mask) v *= leaky_grad_from_act(P.mask[(long)m * P.ld_mask + n]);
+                P.out[(long)m * P.ld_out + n] = v;
+            } else {
+                P.colext[m] = v;
             }
-            if (!row_ok) return;
+        };
+
+        // coalesced output of the staged sub-tile: fully unrolled (compile-time trip counts) so that the shared-memory
+        // reads, mask loads and stores of all rows are independent instructions in flight together
+        auto write_out = [&]() {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                if (c * 16 + j < ncols) {
-                    const int n = nb + j;
-                    float x = v[j];
-                    if (n < n_out) {
-                        x += bias_r[j];
-                        if (P.act == 1) x = leaky(x);
-                        if (P.mask) x *= leaky_grad_from_act(mask_r[j]);
-                        P.out[(long)m * P.ld_out + n] = x;
-                    } else {
-                        P.colext[m] = x;
-                    }
+            for (int cc = 0; cc < 2; ++cc) {
+                if (cc < nchunk && cc * 32 + lane < ncols) {
+#pragma unroll
+                    for (int rr = 0; rr < 32; ++rr)
+                        if (rr < rows) finish(rr, cc, sT[rr * TP + cc * 32 + lane]);
                 }
             }
         };
 
         if (P.splits == 1) {
-#pragma unroll 1
-            for (int c = 0; c * 16 < ncols; ++c) {
-                uint32_t r[16];
-                tmem_ld16(taddr + (uint32_t)(c * 16), r);
-                float v[16];
-#pragma unroll
-                for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
-                finish16(c, v);
-            }
+            write_out();
         } else {
-            // ---- split-K: park the raw partial tile ([128][bn], 16-byte stores), take a ticket; the last CTA of the
-            //      tile sums the partials in split order (deterministic) and runs the epilogue ----
-            float* wt = P.ws + ((long)tile * P.splits + split) * (TC_BM * P.bn) + (q * 32 + lane) * P.bn + c_lo;
-#pragma unroll 1
+            // ---- split-K: park the raw partial tile (thread = row: 16-byte stores into the private workspace),
+            //      take a ticket; the last CTA of the tile sums the partials in split order (deterministic),
+            //      re-stages the sums and runs the same coalesced epilogue ----
+            const long sstride = (long)TC_BM * P.bn;
+            float* wt = P.ws + ((long)tile * P.splits + split) * sstride + (q * 32 + lane) * P.bn + c_lo;
             for (int c = 0; c * 16 < ncols; ++c) {
-                uint32_t r[16];
-                tmem_ld16(taddr + (uint32_t)(c * 16), r);
 #pragma unroll
                 for (int j = 0; j < 16; j += 4)
-                    *reinterpret_cast<uint4*>(wt + c * 16 + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+                    *reinterpret_cast<float4*>(wt + c * 16 + j) =
+                        make_float4(sT[lane * TP + c * 16 + j], sT[lane * TP + c * 16 + j + 1], sT[lane * TP + c * 16 + j + 2],
+                                    sT[lane * TP + c * 16 + j + 3]);
             }
             __threadfence();
             asm volatile("bar.sync 2, %0;" ::"n"(32 * TC_EPI_WARPS) : "memory");
@@ -263,23 +272,36 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
             asm volatile("bar.sync 2, %0;" ::"n"(32 * TC_EPI_WARPS) : "memory");
             if (*s_last) {
                 __threadfence();
-                const float* w0 = P.ws + (long)tile * P.splits * (TC_BM * P.bn) + (q * 32 + lane) * P.bn + c_lo;
-                const long sstride = (long)TC_BM * P.bn;
-#pragma unroll 1
+                const float* w0 = P.ws + (long)tile * P.splits * sstride + (q * 32 + lane) * P.bn + c_lo;
                 for (int c = 0; c * 16 < ncols; ++c) {
-                    float v[16];
+                    float4 acc[4];
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) v[j] = 0.f;
-                    for (int sp = 0; sp < P.splits; ++sp) {
-                        const float4* src = reinterpret_cast<const float4*>(w0 + sp * sstride + c * 16);
-                        const float4 x0 = __ldcg(src), x1 = __ldcg(src + 1), x2 = __ldcg(src + 2), x3 = __ldcg(src + 3);
-                        v[0] += x0.x; v[1] += x0.y; v[2] += x0.z; v[3] += x0.w;
-                        v[4] += x1.x; v[5] += x1.y; v[6] += x1.z; v[7] += x1.w;
-                        v[8] += x2.x; v[9] += x2.y; v[10] += x2.z; v[11] += x2.w;
-                        v[12] += x3.x; v[13] += x3.y; v[14] += x3.z; v[15] += x3.w;
+                    for (int u = 0; u < 4; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int sp0 = 0; sp0 < P.splits; sp0 += 4) {        // 16 loads in flight, added in split order
+                        float4 x[4][4];
+#pragma unroll
+                        for (int d = 0; d < 4; ++d)
+#pragma unroll
+                            for (int u = 0; u < 4; ++u)
+                                x[d][u] = (sp0 + d < P.splits)
+                                              ? __ldcg(reinterpret_cast<const float4*>(w0 + (sp0 + d) * sstride + c * 16) + u)
+                                              : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                        for (int d = 0; d < 4; ++d)
+#pragma unroll
+                            for (int u = 0; u < 4; ++u) {
+                                acc[u].x += x[d][u].x; acc[u].y += x[d][u].y; acc[u].z += x[d][u].z; acc[u].w += x[d][u].w;
+                            }
                     }
-                    finish16(c, v);
+                    __syncwarp();
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        sT[lane * TP + c * 16 + 4 * u + 0] = acc[u].x; sT[lane * TP + c * 16 + 4 * u + 1] = acc[u].y;
+                        sT[lane * TP + c * 16 + 4 * u + 2] = acc[u].z; sT[lane * TP + c * 16 + 4 * u + 3] = acc[u].w;
+                    }
                 }
+                __syncwarp();
+                write_out();
             }
         }
     }
@@ -357,7 +379,8 @@ static void tc_plan(const b200dp_tc_problem* probs, int count, bool can_split, T
         int sp = 1;
         if (can_split && total_tiles < target) {
             sp = target / total_tiles;
-            const int max_sp = nslab / 3 > 0 ? nslab / 3 : 1;          // at least 3 slabs per split
+            const int max_sp = nslab / 6 > 0 ? nslab / 6 : 1;          // at least 6 slabs per split: a split costs a
+                                                                       // partial-tile round trip through L2
             if (sp > max_sp) sp = max_sp;
             if (sp > 16) sp = 16;
             if (sp < 1) sp = 1;
