@@ -1,0 +1,14 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -q --tb=short -p no:cacheprovider -x > gpurun_out/pytest_gpu.log 2>&1
+echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+tail -n 4 gpurun_out/pytest_gpu.log | cut -c1-300
+timeout 300 python bench.py --steps 300 --warmup 30 --config wide_cifar > gpurun_out/bench_wide_n1.log 2>&1
+echo "wide rc=$?" >> gpurun_out/bench_wide_n1.log
+tail -n 2 gpurun_out/bench_wide_n1.log | cut -c1-330
+timeout 300 python bench.py --steps 2000 --warmup 200 > gpurun_out/bench_own_n1.log 2>&1
+tail -n 1 gpurun_out/bench_own_n1.log | cut -c1-330
+KF='regex:conv|gemm|head|reduce_update|pack'
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KF" -c 200 --csv --log-file gpurun_out/launches_wide5.csv \
+    python bench.py --steps 3 --warmup 3 --no-graph --config wide_cifar > gpurun_out/ncu_launch_wide5.log 2>&1
+tail -n 1 gpurun_out/ncu_launch_wide5.log | cut -c1-100

@@ -393,15 +393,15 @@ static void tc_plan(const b200dp_tc_problem* probs, int count, bool can_split, T
     }
 }
 
-static int tc_launch(const b200dp_tc_problem* probs, int count, float* ws, long ws_floats, unsigned* tickets, int n_tickets,
-                     long long* dbg, b200dp_stream_t s);
+static int tc_launch(const b200dp_tc_problem* probs, int count, bool retile, float* ws, long ws_floats, unsigned* tickets,
+                     int n_tickets, long long* dbg, b200dp_stream_t s);
 
 extern "C" int b200dp_tc_gemm_group(const b200dp_tc_problem* probs, int count, b200dp_stream_t s) {
-    return tc_launch(probs, count, nullptr, 0, nullptr, 0, nullptr, s);
+    return tc_launch(probs, count, false, nullptr, 0, nullptr, 0, nullptr, s);
 }
 extern "C" int b200dp_tc_gemm_group_splitk(const b200dp_tc_problem* probs, int count, float* ws, long ws_floats,
                                            uint32_t* tickets, int n_tickets, b200dp_stream_t s) {
-    return tc_launch(probs, count, ws, ws_floats, tickets, n_tickets, nullptr, s);
+    return tc_launch(probs, count, true, ws, ws_floats, tickets, n_tickets, nullptr, s);
 }
 extern "C" long b200dp_tc_gemm_ws_floats(const b200dp_tc_problem* probs, int count, int* n_tickets) {
     if (count < 1 || count > TC_MAX_PROBLEMS) return -1;
@@ -414,15 +414,15 @@ extern "C" long b200dp_tc_gemm_ws_floats(const b200dp_tc_problem* probs, int cou
 // [0] start, [1] setup done, [2] accumulator complete, [3] epilogue done, [4] end,
 // [8+s] producer issued slab s, [16+s] slab s landed (s < 8).
 extern "C" int b200dp_tc_gemm_group_timed(const b200dp_tc_problem* probs, int count, long long* dbg, b200dp_stream_t s) {
-    return tc_launch(probs, count, nullptr, 0, nullptr, 0, dbg, s);
+    return tc_launch(probs, count, false, nullptr, 0, nullptr, 0, dbg, s);
 }
 
-static int tc_launch(const b200dp_tc_problem* probs, int count, float* ws, long ws_floats, unsigned* tickets, int n_tickets,
-                     long long* dbg, b200dp_stream_t s) {
+static int tc_launch(const b200dp_tc_problem* probs, int count, bool retile, float* ws, long ws_floats, unsigned* tickets,
+                     int n_tickets, long long* dbg, b200dp_stream_t s) {
     B200DP_REQUIRE(count >= 1 && count <= TC_MAX_PROBLEMS, "1..4 problems per launch");
     TcPlan pl;
-    tc_plan(probs, count, ws != nullptr && tickets != nullptr, pl);
-    B200DP_REQUIRE(pl.ws_floats <= ws_floats && pl.n_tickets <= n_tickets,
+    tc_plan(probs, count, retile, pl);
+    B200DP_REQUIRE(pl.ws_floats <= ws_floats && pl.n_tickets <= n_tickets && (pl.ws_floats == 0 || (ws && tickets)),
                    "split-K workspace too small: size it with b200dp_tc_gemm_ws_floats");
     TcGroup g;
     memset(&g, 0, sizeof(g));

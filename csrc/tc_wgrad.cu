@@ -20,8 +20,8 @@
 //
 // Replaces the weight/bias-gradient half of the autograd backward of cnn.py:10-15 (train.py:49; cuDNN wgrad).
 //
-// CTA: warps 0-7 stage position chunks (double-buffered when shared memory allows), warp 8 issues the MMAs
-// (uniform control flow, one elected lane), warps 0-3 run the epilogue.
+// CTA: warps 0-15 stage (dZ once per image, the expanded input per position chunk, double-buffered), warp 16 issues
+// the MMAs (uniform control flow, one elected lane), warps 0-3 run the epilogue.
 #include <cuda_bf16.h>
 
 #include "common.cuh"
@@ -29,8 +29,9 @@
 
 namespace b200dp {
 
-constexpr int WG_THREADS = 288;
-constexpr int WG_STAGERS = 256;
+constexpr int WG_NSTAGE = 16;                        // stager warps (latency-bound work: more warps = more in flight)
+constexpr int WG_STAGERS = 32 * WG_NSTAGE;
+constexpr int WG_THREADS = WG_STAGERS + 32;          // + the MMA-issuing warp
 
 __device__ __forceinline__ uint64_t wg_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
     return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) |
@@ -70,11 +71,11 @@ struct WgCfg {
     static constexpr int TAP_SPAN = FIRST ? 0 : 4 * PITCH;
     static constexpr int PA = P + TAP_SPAN;                           // positions held by the A buffer
     static constexpr int A_BYTES = 16 * PA * 16;                      // M = 128 addresses 16 channel groups of 8
-    static constexpr int B_BYTES = KGB * P * 16;
+    static constexpr int B_BYTES = KGB * NPOS * 16;                   // the whole image's output gradient (staged once per image)
     static constexpr int MAXOFF = 4 * PITCH + 4;
     static constexpr int PLANE_PAD = (NCHUNK * P + TAP_SPAN + MAXOFF + 8 + 3) / 4 * 4;
     static constexpr int PLANES_BYTES = CIN * PLANE_PAD * 4 + (FIRST ? CIN * 1024 * 4 : 0);
-    static constexpr int FIXED = 1024 + PLANES_BYTES + 64;
+    static constexpr int FIXED = 1024 + PLANES_BYTES + 64 + 128 * 4;   // + offset table of the expanded channels
     static constexpr int NBUF = (FIXED + 2 * (A_BYTES + B_BYTES) <= 232448) ? 2 : 1;
     static constexpr size_t SMEM = FIXED + (size_t)NBUF * (A_BYTES + B_BYTES);
     static_assert(SMEM <= 232448, "shared memory");
@@ -96,18 +97,22 @@ struct WgArgs {
     const uint8_t* idx;       // [B][COUT][PP] argmax inside the pool window
     float* partials; int partial_stride, off_w, off_b;
     int B, img_per_cta;
+    long long* dbg;           // profiling aid (nullable): CTA 0 writes clock64() stamps to dbg[0..16)
 };
+static long long* g_wg_dbg = nullptr;
+#define WG_STAMP(i) do { if (a.dbg && blockIdx.x == 0 && (threadIdx.x & 31) == 0) a.dbg[i] = clock64(); } while (0)
 
 template <int LAYER, int CIN, int COUT>
 __global__ void __launch_bounds__(WG_THREADS, 1) wg_conv_kernel(const __grid_constant__ WgArgs a) {
     using C = WgCfg<LAYER, CIN, COUT>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
-    uint8_t* sAB = base;                                               // [NBUF]{A: [32][PA][4], B: [KGB][P][4]}
+    uint8_t* sAB = base;                                               // [NBUF] A: [16][PA][8 bf16], then [NBUF] B: [KGB][NPOS][8 bf16]
     float* sPl = reinterpret_cast<float*>(base + (size_t)C::NBUF * (C::A_BYTES + C::B_BYTES));   // [CIN][PLANE_PAD]
     float* sRaw = sPl + CIN * C::PLANE_PAD;                            // layer 1 with 28x28 input: raw planes
     uint64_t* bar_mem = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sPl) + C::PLANES_BYTES);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_mem + 5);
+    int* sOff = reinterpret_cast<int*>(bar_mem + 8);                   // [128] expanded channel -> offset into sPl (-1 ones, -2 zero)
     const uint32_t bars = smem_u32(bar_mem);
     auto staged = [&](int b) { return bars + 8u * b; };                // stagers -> MMA warp (count 256)
     auto drained = [&](int b) { return bars + 8u * (2 + b); };         // MMA warp -> stagers (tcgen05.commit)
@@ -117,19 +122,22 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wg_conv_kernel(const __grid_con
     const int img0 = blockIdx.x * a.img_per_cta;
     const int nimg = max(0, min(a.img_per_cta, a.B - img0));
     const int nchunks = nimg * C::NCHUNK;
+    if (tid == 0) WG_STAMP(0);
 
+    if (tid < 128) sOff[tid] = tid < C::CA - 1 ? C::plane_of(tid) * C::PLANE_PAD + C::off_of(tid) : (tid == C::CA - 1 ? -1 : -2);
     if (tid == 0) {
         for (int b = 0; b < 2; ++b) { mbar_init(staged(b), WG_STAGERS); mbar_init(drained(b), 1); }
         mbar_init(acc_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 8) tmem_alloc(smem_u32(tmem_slot), C::TMEM_COLS);
+    if (warp == WG_NSTAGE) tmem_alloc(smem_u32(tmem_slot), C::TMEM_COLS);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    if (tid == 0) WG_STAMP(1);
 
-    if (warp < 8) {
+    if (warp < WG_NSTAGE) {
         // ================= stagers =================
         for (int ch = 0; ch < nchunks; ++ch) {
             const int ii = ch / C::NCHUNK, ck = ch - ii * C::NCHUNK, img = img0 + ii;
@@ -161,54 +169,51 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wg_conv_kernel(const __grid_con
                 }
                 asm volatile("bar.sync 1, %0;" ::"n"(WG_STAGERS) : "memory");
             }
+            if (tid == 0 && ch == 0) WG_STAMP(2);                       // first image's planes ready
             // ---- wait until the tensor core has finished reading this buffer (chunk ch - NBUF) ----
             if (ch >= C::NBUF) mbar_wait(drained(b), ((ch / C::NBUF) - 1) & 1);
-            uint4* sA = reinterpret_cast<uint4*>(sAB + (size_t)b * (C::A_BYTES + C::B_BYTES));
-            uint4* sB = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(sA) + C::A_BYTES);
+            const int ib = C::NBUF == 2 ? (ii & 1) : 0;                  // B buffer of this image
+            uint4* sA = reinterpret_cast<uint4*>(sAB + (size_t)b * C::A_BYTES);
+            uint4* sB = reinterpret_cast<uint4*>(sAB + (size_t)C::NBUF * C::A_BYTES + (size_t)ib * C::B_BYTES);
             const int p0 = ck * C::P;
-            // A: warp w expands channel groups w, w+8, ...; lanes run over positions (conflict-free 16-byte stores)
-            for (int cg = warp; cg < C::KGA; cg += 8) {
-                int off[8];
-#pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    const int cc = cg * 8 + q;
-                    off[q] = cc < C::CA - 1 ? C::plane_of(cc) * C::PLANE_PAD + C::off_of(cc) + p0 : (cc == C::CA - 1 ? -1 : -2);
-                }
-                uint4* dst = sA + (size_t)cg * C::PA;
-#pragma unroll 2
-                for (int p = lane; p < C::PA; p += 32) {
-                    float v[8];
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) v[q] = off[q] >= 0 ? sPl[off[q] + p] : (off[q] == -1 ? 1.f : 0.f);
-                    dst[p] = make_uint4(wg_pack_bf16(v[0], v[1]), wg_pack_bf16(v[2], v[3]), wg_pack_bf16(v[4], v[5]),
-                                        wg_pack_bf16(v[6], v[7]));
+            if (ck == 0) {
+                // B, once per image: zero, then scatter every pooled gradient to its argmax position (pool-bwd) with
+                // LeakyReLU' applied.  (The wait above covers this buffer too: chunk ch-NBUF is later than every chunk
+                // of the image that last used it.)
+                for (int i = tid; i < C::KGB * C::NPOS; i += WG_STAGERS) sB[i] = make_uint4(0u, 0u, 0u, 0u);
+                asm volatile("bar.sync 1, %0;" ::"n"(WG_STAGERS) : "memory");
+                __nv_bfloat16* sBh = reinterpret_cast<__nv_bfloat16*>(sB);
+                const long o0 = (long)img * COUT * C::PP;
+#pragma unroll 4
+                for (int i = tid; i < COUT * C::PP; i += WG_STAGERS) {
+                    const int oc = i / C::PP, rem = i - oc * C::PP;
+                    const int py = rem / C::PW, px = rem - py * C::PW;
+                    const int k = a.idx[o0 + i];
+                    float g = a.g[o0 + i];
+                    if (a.act) g *= leaky_grad_from_act(a.act[(long)img * a.ld_act + i]);
+                    const int pos = (2 * py + (k >> 1)) * C::PITCH + 2 * px + (k & 1);
+                    sBh[((oc >> 3) * C::NPOS + pos) * 8 + (oc & 7)] = __float2bfloat16_rn(g);
                 }
             }
-            // B: zero, then scatter the pooled gradients of this chunk's rows to their argmax positions
-            for (int i = tid; i < C::KGB * C::P; i += WG_STAGERS) sB[i] = make_uint4(0u, 0u, 0u, 0u);
-            asm volatile("bar.sync 1, %0;" ::"n"(WG_STAGERS) : "memory");
-            {
-                constexpr int ROWS = C::P / C::PITCH;                      // image rows per chunk (layer 1: 4; layer 2: all)
-                constexpr int PY_PER = C::FIRST ? ROWS / 2 : C::PW;        // pooled rows per chunk
-                const int py0 = C::FIRST ? ck * PY_PER : 0;
-                const int cells = COUT * PY_PER * C::PW;
-                __nv_bfloat16* sBh = reinterpret_cast<__nv_bfloat16*>(sB);
-                for (int i = tid; i < cells; i += WG_STAGERS) {
-                    const int oc = i / (PY_PER * C::PW), rem = i - oc * (PY_PER * C::PW);
-                    const int py = py0 + rem / C::PW, px = rem - (rem / C::PW) * C::PW;
-                    if (py < C::PW) {
-                        const long o = ((long)img * COUT + oc) * C::PP + py * C::PW + px;
-                        const int k = a.idx[o];
-                        float g = a.g[o];
-                        if (a.act) g *= leaky_grad_from_act(a.act[(long)img * a.ld_act + oc * C::PP + py * C::PW + px]);
-                        const int pos = (2 * py + (k >> 1)) * C::PITCH + 2 * px + (k & 1) - p0;
-                        sBh[((oc >> 3) * C::P + pos) * 8 + (oc & 7)] = __float2bfloat16_rn(g);
-                    }
+            if (tid == 0 && ch == 0) WG_STAMP(3);                       // first image's dZ staged
+            // A, per chunk: work item = (channel group, block of 32 positions), dealt round-robin to the 8 warps;
+            // lanes run over positions (conflict-free 16-byte stores)
+            constexpr int PBLK = (C::PA + 31) / 32;
+            for (int item = warp; item < C::KGA * PBLK; item += WG_NSTAGE) {
+                const int cg = item / PBLK, p = (item - cg * PBLK) * 32 + lane;
+                const int4 o0 = reinterpret_cast<const int4*>(sOff)[cg * 2], o1 = reinterpret_cast<const int4*>(sOff)[cg * 2 + 1];
+                if (p < C::PA) {
+                    const float* src = sPl + p0 + p;
+                    auto tap = [&](int o) { return o >= 0 ? src[o] : (o == -1 ? 1.f : 0.f); };
+                    sA[(size_t)cg * C::PA + p] = make_uint4(wg_pack_bf16(tap(o0.x), tap(o0.y)), wg_pack_bf16(tap(o0.z), tap(o0.w)),
+                                                            wg_pack_bf16(tap(o1.x), tap(o1.y)), wg_pack_bf16(tap(o1.z), tap(o1.w)));
                 }
             }
             fence_proxy_async_smem();
             mbar_arrive(staged(b));
+            if (tid == 0 && ch < 2) WG_STAMP(4 + ch);                  // chunk 0 / 1 staged
         }
+        if (tid == 0) WG_STAMP(6);                                     // everything staged
     } else {
         // ================= MMA issuer (warp 8): uniform loop, one elected lane =================
         const bool leader = wg_elect();
@@ -218,9 +223,11 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wg_conv_kernel(const __grid_con
             const int b = C::NBUF == 2 ? (ch & 1) : 0;
             mbar_wait(staged(b), (ch / C::NBUF) & 1);
             tc_fence_after();
-            const uint32_t sa = smem_u32(sAB + (size_t)b * (C::A_BYTES + C::B_BYTES)), sb = sa + C::A_BYTES;
+            const int ii = ch / C::NCHUNK, ck = ch - ii * C::NCHUNK;
+            const uint32_t sa = smem_u32(sAB + (size_t)b * C::A_BYTES);
+            const uint32_t sb = smem_u32(sAB + (size_t)C::NBUF * C::A_BYTES + (size_t)(C::NBUF == 2 ? (ii & 1) : 0) * C::B_BYTES);
             const uint64_t adesc = wg_desc(sa, 128u, C::PA * 16u);      // LBO: next 8 positions; SBO: next channel group
-            const uint64_t bdesc = wg_desc(sb, 128u, C::P * 16u);
+            const uint64_t bdesc = wg_desc(sb, 128u, C::NPOS * 16u) + (uint64_t)(ck * C::P);
             if (leader) {
 #pragma unroll 1
                 for (int j = 0; j < C::P / 16; ++j) {           // 16 positions (two 8-row K groups, LBO apart) per MMA
@@ -233,47 +240,59 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wg_conv_kernel(const __grid_con
                 if (ch == nchunks - 1) umma_commit(acc_bar);
             }
             __syncwarp();
+            if (ch == 0) WG_STAMP(9);
         }
+        WG_STAMP(10);
     }
 
-    // ================= epilogue (warps 0-3): thread = accumulator row = expanded channel =================
-    if (warp < 4) {
+    // ================= epilogue: warps 0-3 read the accumulators (thread = row = expanded channel), 16 columns at a
+    // time, into shared memory (the operand buffers are idle now); all 16 warps then write the partial row in the
+    // arena's [oc][ic][ky][kx] order with consecutive lanes on consecutive addresses.  (Storing straight from the
+    // accumulator layout puts a warp's 32 lanes on ~7 different lines per instruction; that was half of this kernel.) ====
+    if (warp < WG_NSTAGE) {
         float* row = a.partials + (long)blockIdx.x * a.partial_stride;
-        const int m = warp * 32 + lane;
         if (nchunks > 0) {
             mbar_wait(acc_bar, 0);
             tc_fence_after();
         }
-        constexpr int KW = CIN * 25;
-        // destination of row m inside dW[oc][ic][ky][kx] for tap t (layer 2: m = (ic,kx), t = ky)
+        if (tid == 0) WG_STAMP(7);
+        constexpr int KW = CIN * 25, TP = 17;
+        float* sT = reinterpret_cast<float*>(sAB);                      // [NTAP][128][TP]
+        const int m = (warp & 3) * 32 + lane;
 #pragma unroll 1
-        for (int t = 0; t < C::NTAP; ++t) {
-            int wofs = -1;
-            if (m < C::CA - 1) wofs = C::FIRST ? m : (m / 5) * 25 + t * 5 + (m % 5);
-            const bool is_bias = (m == C::CA - 1) && t == 0;
+        for (int n0 = 0; n0 < C::NP; n0 += 16) {
+            if (warp < 4) {
 #pragma unroll 1
-            for (int n0 = 0; n0 < C::NP; n0 += 16) {
-                uint32_t v[16];
-                if (nchunks > 0) {
-                    tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * C::NP + n0), v);
-                } else {
+                for (int t = 0; t < C::NTAP; ++t) {
+                    uint32_t v[16];
+                    if (nchunks > 0) {
+                        tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * C::NP + n0), v);
+                    } else {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) v[j] = 0u;
-                }
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const int n = n0 + j;
-                    if (n < COUT) {
-                        if (wofs >= 0) row[a.off_w + n * KW + wofs] = __uint_as_float(v[j]);
-                        else if (is_bias) row[a.off_b + n] = __uint_as_float(v[j]);
+                        for (int j = 0; j < 16; ++j) v[j] = 0u;
                     }
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) sT[(t * 128 + m) * TP + j] = __uint_as_float(v[j]);
                 }
             }
+            asm volatile("bar.sync 1, %0;" ::"n"(WG_STAGERS) : "memory");
+            for (int i = tid; i < 16 * KW; i += WG_STAGERS) {
+                const int n = i / KW, k = i - n * KW;
+                if (n0 + n < COUT) {
+                    int t, mm;
+                    if constexpr (C::FIRST) { t = 0; mm = k; }
+                    else { const int ic = k / 25, r = k - ic * 25; t = r / 5; mm = ic * 5 + (r - t * 5); }
+                    row[a.off_w + (n0 + n) * KW + k] = sT[(t * 128 + mm) * TP + n];
+                }
+            }
+            if (tid < 16 && n0 + tid < COUT) row[a.off_b + n0 + tid] = sT[(C::CA - 1) * TP + tid];   // ones row, tap 0
+            asm volatile("bar.sync 1, %0;" ::"n"(WG_STAGERS) : "memory");
         }
     }
+    if (tid == 0) WG_STAMP(8);
     tc_fence_before();
     __syncthreads();
-    if (warp == 8) {
+    if (warp == WG_NSTAGE) {
         tc_fence_after();
         tmem_dealloc(tmem, C::TMEM_COLS);
     }
@@ -288,7 +307,9 @@ static int wg_launch(const WgArgs& a, int rows, cudaStream_t s) {
         B200DP_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
         attr_set = true;
     }
-    kern<<<rows, WG_THREADS, C::SMEM, s>>>(a);
+    WgArgs b = a;
+    b.dbg = g_wg_dbg;
+    kern<<<rows, WG_THREADS, C::SMEM, s>>>(b);
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }
@@ -296,6 +317,10 @@ static int wg_launch(const WgArgs& a, int rows, cudaStream_t s) {
 }  // namespace b200dp
 
 using namespace b200dp;
+
+// Profiling aid (see b200dp_tcw_set_debug): stamps 0 start, 1 set-up, 2 planes of image 0, 3 dZ of image 0, 4/5 chunk 0/1
+// staged, 6 all staged, 7 accumulators ready, 8 epilogue done, 9 first chunk's MMAs issued, 10 all issued.
+extern "C" void b200dp_tcw_wgrad_set_debug(long long* dbg) { g_wg_dbg = dbg; }
 
 extern "C" int b200dp_tcw_conv_wgrad_num_partials(b200dp_dims d) {
     int n = (d.batch + 1) / 2;
@@ -308,7 +333,7 @@ extern "C" int b200dp_tcw_conv_wgrad(int layer, const void* x, int in_is_u8, flo
                                      int partial_stride, int off_w, int off_b, b200dp_dims d, b200dp_stream_t s) {
     const int rows = b200dp_tcw_conv_wgrad_num_partials(d);
     const int ipc = (d.batch + rows - 1) / rows;
-    WgArgs a{x, in_is_u8, d.in_hw, mean, std, g, act, ld_act, idx, partials, partial_stride, off_w, off_b, d.batch, ipc};
+    WgArgs a{x, in_is_u8, d.in_hw, mean, std, g, act, ld_act, idx, partials, partial_stride, off_w, off_b, d.batch, ipc, nullptr};
     if (layer == 2) {
         if (d.c1 == 24 && d.c2 == 64) return wg_launch<2, 24, 64>(a, rows, (cudaStream_t)s);
         if (d.c1 == 6 && d.c2 == 16) return wg_launch<2, 6, 16>(a, rows, (cudaStream_t)s);
