@@ -36,9 +36,9 @@ MAX_WORLD = 8
 ALGO_CODES = {"oneshot": 0, "twoshot": 1, "nvls": 2}
 # Measured cross-over (profiles/allreduce_sweep.md).  One-shot pulls (world-1) x bytes into every rank but needs a
 # single handshake; two-shot / NVLS move 2(world-1)/world x bytes with two.  With 2 ranks the byte counts are
-# equal, so one-shot always wins; at 8 ranks it wins up to 4 MB.
+# equal, so one-shot always wins; at 8 ranks it wins up to ~2 MB (1 MB: 35 vs 39 us, 4 MB: 70 vs 45 us NVLS).
 def oneshot_max_bytes(world: int) -> int:
-    return (1 << 62) if world <= 2 else (32 << 20) // world
+    return (1 << 62) if world <= 2 else (16 << 20) // world
 
 
 class P2PComm:
