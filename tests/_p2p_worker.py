@@ -44,3 +44,37 @@ def train_native(ctx, cfg):
         torch.save(out, os.path.join(cfg["out"], f"native_{cfg['tag']}.pt"))
     dist.barrier()
     st.close()
+
+
+def train_epochs(ctx, cfg):
+    """Two epochs through Trainer.train_epoch on this rank's shard, with the native step pump or the Python loop;
+    optionally the 4x-wide model on the tensor-core path."""
+    import torch.distributed as dist
+    from b200dp.data.shard import shard_for_rank
+    from b200dp.data.synthetic import CIFAR_SPEC, MNIST_SPEC, PinnedRingLoader, SyntheticImages
+    from b200dp.engine import Trainer
+    from b200dp.models.fused import NativeStepper
+    from b200dp.models.lenet import CIFAR_WIDE_LENET, MNIST_LENET
+    from b200dp.optim.flat import OptHyper
+    from b200dp.utils.logging import RankLogger
+
+    wide = cfg.get("wide", False)
+    mcfg, spec = (CIFAR_WIDE_LENET, CIFAR_SPEC) if wide else (MNIST_LENET, MNIST_SPEC)
+    torch.manual_seed(cfg["seed"])
+    b = cfg["per_rank_batch"]
+    base = SyntheticImages(cfg["n"], spec, seed=3)
+    sh = shard_for_rank(base, ctx.rank, ctx.world_size)
+    loader = PinnedRingLoader(base.images, base.targets, *sh.bounds(), b, spec, shuffle=True, fmt="u8",
+                              device=ctx.device, seed=17 * ctx.rank, drop_last=True)
+    st = NativeStepper(ctx, mcfg, OptHyper("adadelta", lr=0.1), batch=b, loss_mode="ref", spec=spec, graph=True)
+    tr = Trainer(ctx, st, RankLogger(False, None), log_interval=4, no_pump=cfg["no_pump"])
+    for e in (1, 2):
+        tr.train_epoch(loader, e)
+    torch.cuda.synchronize()
+    st.check_error()
+    out = {"div": st.replica_divergence(), "pumped": tr._pump_for(loader) is not None, "gen": int(st.step_counter[0]),
+           "param": st.arena.param.detach().cpu().clone(), "steps": tr.global_step}
+    if ctx.rank == 0:
+        torch.save(out, os.path.join(cfg["out"], f"epochs_{cfg['tag']}.pt"))
+    dist.barrier()
+    st.close()

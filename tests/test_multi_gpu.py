@@ -75,3 +75,21 @@ def test_p2p_deterministic_under_skew(tmp_path, world):
     for k in outs["plain"]["params"]:
         assert torch.equal(outs["plain"]["params"][k], outs["skew"]["params"][k]), k
         assert torch.equal(outs["plain"]["params"][k], outs["nograph"]["params"][k]), k
+
+
+@pytest.mark.parametrize("world,wide", [(2, False), (2, True), (8, False)])
+def test_pumped_epochs_match_python_loop_multi_gpu(tmp_path, world, wide):
+    """The native step pump drives every rank's epoch (graphs with the fused P2P reduce+update inside): same
+    parameters, bit for bit, as the Python loop, and identical replicas."""
+    _need(world)
+    from _p2p_worker import train_epochs
+    from b200dp.parallel import launch
+    base = {"seed": 5, "per_rank_batch": 32, "n": 32 * 9 * world, "out": str(tmp_path), "wide": wide}
+    outs = {}
+    for tag, no_pump in (("pump", False), ("py", True)):
+        launch.spawn(train_epochs, dict(base, tag=tag, no_pump=no_pump), world, backend="nccl", use_cuda=True, port=0)
+        outs[tag] = torch.load(os.path.join(tmp_path, f"epochs_{tag}.pt"))
+        assert outs[tag]["div"] == 0.0
+        assert outs[tag]["gen"] == outs[tag]["steps"] == 18
+    assert outs["pump"]["pumped"] and not outs["py"]["pumped"]
+    assert torch.equal(outs["pump"]["param"], outs["py"]["param"])
