@@ -1,0 +1,11 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_kernels_gpu.py tests/test_pump_gpu.py -m gpu -q --tb=short -p no:cacheprovider -x > gpurun_out/pytest_k.log 2>&1
+echo "pytest rc=$?" >> gpurun_out/pytest_k.log
+tail -n 4 gpurun_out/pytest_k.log | cut -c1-300
+timeout 300 python bench.py --steps 2000 --warmup 200 > gpurun_out/bench_own_n1.log 2>&1
+tail -n 1 gpurun_out/bench_own_n1.log | cut -c1-330
+KF='regex:conv|gemm|head|reduce_update|pack'
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KF" -c 100 --csv --log-file gpurun_out/launches_lenet2.csv \
+    python bench.py --steps 3 --warmup 3 --no-graph > gpurun_out/ncu_launch_lenet2.log 2>&1
+tail -n 1 gpurun_out/ncu_launch_lenet2.log | cut -c1-100

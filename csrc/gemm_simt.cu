@@ -4,15 +4,21 @@
 //
 // Replaces reference cnn.py:16-17 (conv3 on a 5x5 map == GEMM), cnn.py:20-21 (FC.0) and their
 // autograd backward (train.py:49).  The batch dimension here is 256, so these GEMMs are a few
-// MFLOP each: the design goal is few launches and enough CTAs, not MMA rate.  A CTA owns a 32x32
-// output tile; its 256 threads are four k-groups of 64 (4x4 micro-tile each) that split every
-// 32-deep k-slab and are summed in fixed order at the end (deterministic, no atomics).
+// MFLOP each: the design goal is few launches and enough CTAs, not MMA rate.  A CTA owns a 16x16
+// output tile (with 32x32 tiles the K=400 layer ran on 32 of the 148 SMs, each CTA grinding through ~3K
+// dependent instructions per thread; 16x16 tiles give 128 CTAs with a third of the work per thread); its 256
+// threads are four k-groups of 64 (2x2 micro-tile each) that split every 32-deep k-slab and are summed in fixed
+// order at the end (deterministic, no atomics).
 // The tensor-core path for the wide model is tc_gemm.cu.
 #include "common.cuh"
 
 namespace b200dp {
 
-constexpr int BM = 32, BN = 32, BK = 32, KG = 4, GEMM_NT = 256;
+constexpr int BM = 16, BN = 16, BK = 32, KG = 4, GEMM_NT = 256;
+constexpr int TM = BM / 8, TN = BN / 8;            // micro-tile of a thread (8x8 threads per k-group)
+constexpr int LT = BM * BK / GEMM_NT;               // operand-tile elements per thread
+constexpr int OT = (BM * BN + GEMM_NT - 1) / GEMM_NT;   // output elements per thread in the epilogue
+static_assert(BM == BN && BM * BK % GEMM_NT == 0, "tile shape");
 
 struct GemmProblem {
     const float* A; const float* B; float* C;
@@ -30,30 +36,30 @@ struct GemmGroup {
 };
 
 __device__ __forceinline__ void load_tile(const float* __restrict__ P, long s_mn, long s_k, int mn0, int k0,
-                                          int MN, int K, float (&r)[4], int tid) {
-    // 32x32 tile, 4 elements per thread.  Pick the thread->element map that makes the unit-stride
+                                          int MN, int K, float (&r)[LT], int tid) {
+    // BM x BK tile, LT elements per thread.  Pick the thread->element map that makes the unit-stride
     // dimension the fastest-varying one across a warp (coalesced either way).
     if (s_k == 1) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            int e = tid + j * GEMM_NT, mn = e >> 5, k = e & 31;
+        for (int j = 0; j < LT; ++j) {
+            int e = tid + j * GEMM_NT, mn = e / BK, k = e % BK;
             r[j] = (mn0 + mn < MN && k0 + k < K) ? P[(long)(mn0 + mn) * s_mn + (k0 + k)] : 0.f;
         }
     } else {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            int e = tid + j * GEMM_NT, k = e >> 5, mn = e & 31;
+        for (int j = 0; j < LT; ++j) {
+            int e = tid + j * GEMM_NT, k = e / BM, mn = e % BM;
             r[j] = (mn0 + mn < MN && k0 + k < K) ? P[(long)(mn0 + mn) * s_mn + (long)(k0 + k) * s_k] : 0.f;
         }
     }
 }
-__device__ __forceinline__ void store_tile(float (*S)[BM + 1], long s_k, const float (&r)[4], int tid) {
+__device__ __forceinline__ void store_tile(float (*S)[BM + 1], long s_k, const float (&r)[LT], int tid) {
     if (s_k == 1) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { int e = tid + j * GEMM_NT; S[e & 31][e >> 5] = r[j]; }
+        for (int j = 0; j < LT; ++j) { int e = tid + j * GEMM_NT; S[e % BK][e / BK] = r[j]; }
     } else {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { int e = tid + j * GEMM_NT; S[e >> 5][e & 31] = r[j]; }
+        for (int j = 0; j < LT; ++j) { int e = tid + j * GEMM_NT; S[e / BM][e % BM] = r[j]; }
     }
 }
 
@@ -83,17 +89,19 @@ __global__ void __launch_bounds__(GEMM_NT) gemm_group_kernel(GemmGroup g) {
     const int tid = threadIdx.x;
     const int kg = tid >> 6;           // k-group 0..3
     const int t64 = tid & 63;
-    const int tx = t64 & 7, ty = t64 >> 3;   // 8x8 threads, 4x4 outputs each
+    const int tx = t64 & 7, ty = t64 >> 3;   // 8x8 threads, TM x TN outputs each
     const bool want_cs = (p.colsum != nullptr) && (tn == 0);
 
-    float acc[4][4];
+    float acc[TM][TN];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < TM; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-    float cs[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+    float cs[TM];
+#pragma unroll
+    for (int i = 0; i < TM; ++i) cs[i] = 0.f;
 
-    float ra[4], rb[4];
+    float ra[LT], rb[LT];
     const int nslab = (p.K + BK - 1) / BK;
     load_tile(p.A, p.sAm, p.sAk, m0, 0, p.M, p.K, ra, tid);
     load_tile(p.B, p.sBn, p.sBk, n0, 0, p.N, p.K, rb, tid);
@@ -108,18 +116,18 @@ __global__ void __launch_bounds__(GEMM_NT) gemm_group_kernel(GemmGroup g) {
 #pragma unroll
         for (int kk = 0; kk < BK / KG; ++kk) {
             const int k = kg * (BK / KG) + kk;
-            float av[4], bv[4];
+            float av[TM], bv[TN];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) av[i] = As[k][ty * 4 + i];
+            for (int i = 0; i < TM; ++i) av[i] = As[k][ty * TM + i];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) bv[j] = Bs[k][tx * 4 + j];
+            for (int j = 0; j < TN; ++j) bv[j] = Bs[k][tx * TN + j];
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < TM; ++i)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+                for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
             if (want_cs && tx == 0) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) cs[i] += av[i];
+                for (int i = 0; i < TM; ++i) cs[i] += av[i];
             }
         }
         __syncthreads();
@@ -127,18 +135,18 @@ __global__ void __launch_bounds__(GEMM_NT) gemm_group_kernel(GemmGroup g) {
 
     // ---- fixed-order reduction over the four k-groups + epilogue ----
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < TM; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) Red[kg][ty * 4 + i][tx * 4 + j] = acc[i][j];
+        for (int j = 0; j < TN; ++j) Red[kg][ty * TM + i][tx * TN + j] = acc[i][j];
     if (want_cs && tx == 0) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) RedCs[kg][ty * 4 + i] = cs[i];
+        for (int i = 0; i < TM; ++i) RedCs[kg][ty * TM + i] = cs[i];
     }
     __syncthreads();
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const int e = tid + j * GEMM_NT, m = e >> 5, n = e & 31;
-        if (m0 + m < p.M && n0 + n < p.N) {
+    for (int j = 0; j < OT; ++j) {
+        const int e = tid + j * GEMM_NT, m = e / BN, n = e % BN;
+        if (e < BM * BN && m0 + m < p.M && n0 + n < p.N) {
             float v = ((Red[0][m][n] + Red[1][m][n]) + Red[2][m][n]) + Red[3][m][n];
             if (p.bias) v += p.bias[n0 + n];
             if (p.act == 1) v = leaky(v);
