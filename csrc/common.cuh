@@ -31,6 +31,29 @@ void set_last_error(const char* fmt, ...);
         }                                                                               \
     } while (0)
 
+// ---- programmatic dependent launch (PDL) ----------------------------------------------------------
+// The step is a chain of ~10 short kernels; between two of them the GPU idles for the ~1-2 us it takes to
+// drain one grid and schedule the next.  Launched with the programmatic-stream-serialization attribute, a
+// kernel's CTAs may become resident while its predecessor is still running (as soon as every predecessor CTA
+// has executed pdl_trigger); they then block in pdl_wait until the predecessor has completed and its memory
+// is visible.  Every kernel calls pdl_wait at its very top, before touching global memory, so the data
+// dependencies are exactly those of ordinary stream order; pdl_trigger sits just before a kernel's final
+// stores (triggering at the top made the step SLOWER: early dependents hold registers and CTA slots the
+// running grid needs), so only the scheduling gap is hidden.  Captured into CUDA graphs as programmatic edges.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <class Kern, class Args>
+static inline cudaError_t launch_pdl(Kern kern, dim3 grid, dim3 block, size_t smem, cudaStream_t s, const Args& args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, args);
+}
+
 __device__ __forceinline__ float leaky(float v) { return v > 0.f ? v : LEAKY_SLOPE * v; }
 // derivative of LeakyReLU evaluated from the *activated* value (sign is preserved)
 __device__ __forceinline__ float leaky_grad_from_act(float a) { return a > 0.f ? 1.f : LEAKY_SLOPE; }

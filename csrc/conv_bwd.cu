@@ -49,6 +49,7 @@ struct ConvBwdCfg {
 
 template <int C0, int C1, int C2>
 __global__ void __launch_bounds__(CB_NT, 2) conv_bwd_kernel(ConvBwdArgs a) {
+    pdl_wait();
     using C = ConvBwdCfg<C0, C1, C2>;
     extern __shared__ __align__(16) float smem[];
     float* sX0 = smem;
@@ -205,6 +206,7 @@ __global__ void __launch_bounds__(CB_NT, 2) conv_bwd_kernel(ConvBwdArgs a) {
     }
 
     // ---- one partial row per CTA ----
+    pdl_trigger();   // late: see common.cuh
     float* row = a.partials + (long)blockIdx.x * a.partial_stride;
 #pragma unroll
     for (int j = 0; j < C::W2_PER_THREAD; ++j) {
@@ -251,7 +253,7 @@ extern "C" int b200dp_conv_bwd(const void* x, int in_is_u8, float mean, float st
         B200DP_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
         attr_done = true;
     }
-    kern<<<num_partials_for(d.batch), CB_NT, C::SMEM, (cudaStream_t)s>>>(a);
+    B200DP_CHECK(launch_pdl(kern, dim3(num_partials_for(d.batch)), dim3(CB_NT), C::SMEM, (cudaStream_t)s, a));
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }

@@ -37,6 +37,7 @@ struct ConvFwdArgs {
 template <int CIN, int COUT, int IN_W, int OCT, int GPB, int IPB, bool FIRST>
 __global__ void __launch_bounds__(ConvFwdCfg<CIN, COUT, IN_W, OCT, GPB, IPB, FIRST>::NT)
 conv5_pool_fwd_kernel(ConvFwdArgs a) {
+    pdl_wait();
     using C = ConvFwdCfg<CIN, COUT, IN_W, OCT, GPB, IPB, FIRST>;
     extern __shared__ __align__(16) float smem[];
     float* sIn = smem;                                   // [IPB][CIN][PLANE]
@@ -116,6 +117,7 @@ conv5_pool_fwd_kernel(ConvFwdArgs a) {
         }
     }
 
+    pdl_trigger();   // late: the next kernel's CTAs become resident while this grid stores its results
     // ---- epilogue: bias + LeakyReLU + 2x2 max (first max wins, like torch) ----
 #pragma unroll
     for (int o = 0; o < OCT; ++o) {
@@ -145,7 +147,7 @@ static int launch_conv_fwd(const ConvFwdArgs& a, cudaStream_t s) {
         attr_done = true;
     }
     dim3 grid((a.B + IPB - 1) / IPB, COUT / C::COUT_BLK);
-    kern<<<grid, C::NT, smem, s>>>(a);
+    B200DP_CHECK(launch_pdl(kern, dim3(grid), dim3(C::NT), smem, s, a));
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }

@@ -64,6 +64,7 @@ __device__ __forceinline__ void store_tile(float (*S)[BM + 1], long s_k, const f
 }
 
 __global__ void __launch_bounds__(GEMM_NT) gemm_group_kernel(GemmGroup g) {
+    pdl_wait();
     __shared__ float As[BK][BM + 1];
     __shared__ float Bs[BK][BN + 1];
     __shared__ float Red[KG][BM][BN + 1];
@@ -133,6 +134,7 @@ __global__ void __launch_bounds__(GEMM_NT) gemm_group_kernel(GemmGroup g) {
         __syncthreads();
     }
 
+    pdl_trigger();   // late: see common.cuh
     // ---- fixed-order reduction over the four k-groups + epilogue ----
 #pragma unroll
     for (int i = 0; i < TM; ++i)
@@ -168,7 +170,7 @@ static int launch_group(GemmGroup& g, cudaStream_t s) {
         total += ((p.M + BM - 1) / BM) * p.tiles_n;
     }
     if (total == 0) return 0;
-    gemm_group_kernel<<<total, GEMM_NT, 0, s>>>(g);
+    B200DP_CHECK(launch_pdl(gemm_group_kernel, dim3(total), dim3(GEMM_NT), 0, s, g));
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }

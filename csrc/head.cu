@@ -26,6 +26,7 @@ struct HeadTailArgs {
 };
 
 __global__ void __launch_bounds__(HT_ROWS * 32) head_tail_kernel(HeadTailArgs a) {
+    pdl_wait();
     extern __shared__ float sW[];          // [ncls][F1] then bias[ncls]
     float* sBias = sW + a.ncls * a.F1;
     __shared__ int sLast;
@@ -111,6 +112,7 @@ __global__ void __launch_bounds__(HT_ROWS * 32) head_tail_kernel(HeadTailArgs a)
 
     // ---- last CTA: fixed-order batch reduction (deterministic) ----
     __threadfence();
+    pdl_trigger();   // late: see common.cuh
     __syncthreads();
     if (tid == 0) sLast = (atomicAdd(a.ticket, 1) == (int)gridDim.x - 1);
     __syncthreads();
@@ -164,7 +166,7 @@ extern "C" int b200dp_head_tail(const float* h1, const float* w, const float* b,
                    ld_h1 > 0 ? ld_h1 : F1, ld_dlogits > 0 ? ld_dlogits : ncls};
     const int grid = (B + HT_ROWS - 1) / HT_ROWS;
     const size_t smem = (size_t)(ncls * F1 + ncls) * sizeof(float);
-    head_tail_kernel<<<grid, HT_ROWS * 32, smem, (cudaStream_t)s>>>(a);
+    B200DP_CHECK(launch_pdl(head_tail_kernel, dim3(grid), dim3(HT_ROWS * 32), smem, (cudaStream_t)s, a));
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }
