@@ -137,6 +137,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
     if (threadIdx.x == 0) TC_STAMP(1);
+    pdl_wait();      // set-up above overlaps the previous kernel's tail (common.cuh)
 
     if (warp == 0) {
         // ================= TMA producer =================
@@ -196,6 +197,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
         if (threadIdx.x == 64) TC_STAMP(2);          // accumulator complete
+        pdl_trigger();
         const int q = warp & 3;
         const int h = (warp - 2) >> 2;
         const int half = P.bn >> 1, c_lo = h * half;          // this warp's columns [c_lo, c_lo + half) of the tile
@@ -457,7 +459,7 @@ static int tc_launch(const b200dp_tc_problem* probs, int count, bool retile, flo
         B200DP_CHECK(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
         attr_done = true;
     }
-    tc_gemm_kernel<<<total, TC_THREADS, TC_SMEM, (cudaStream_t)s>>>(g);
+    B200DP_CHECK(launch_pdl(tc_gemm_kernel, dim3(total), dim3(TC_THREADS), TC_SMEM, (cudaStream_t)s, g));
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }

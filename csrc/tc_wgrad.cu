@@ -136,6 +136,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wg_conv_kernel(const __grid_con
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     if (tid == 0) WG_STAMP(1);
+    pdl_wait();      // set-up above overlaps the previous kernel's tail (common.cuh)
 
     if (warp < WG_NSTAGE) {
         // ================= stagers =================
@@ -255,6 +256,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wg_conv_kernel(const __grid_con
             mbar_wait(acc_bar, 0);
             tc_fence_after();
         }
+        pdl_trigger();
         if (tid == 0) WG_STAMP(7);
         constexpr int KW = CIN * 25, TP = 17;
         float* sT = reinterpret_cast<float*>(sAB);                      // [NTAP][128][TP]
@@ -309,7 +311,7 @@ static int wg_launch(const WgArgs& a, int rows, cudaStream_t s) {
     }
     WgArgs b = a;
     b.dbg = g_wg_dbg;
-    kern<<<rows, WG_THREADS, C::SMEM, s>>>(b);
+    B200DP_CHECK(launch_pdl(kern, dim3(rows), dim3(WG_THREADS), C::SMEM, s, b));
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }

@@ -251,6 +251,7 @@ __global__ void __launch_bounds__(WIN_THREADS, 1) win_conv_kernel(const __grid_c
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     if (tid == 0) WIN_STAMP(1);
+    pdl_wait();      // barrier set-up and TMEM allocation above overlap the previous kernel's tail (common.cuh)
 
     auto load_tap = [&](int t) {
         const int s = t % C::RING;
@@ -299,6 +300,7 @@ __global__ void __launch_bounds__(WIN_THREADS, 1) win_conv_kernel(const __grid_c
         // pixel: row 4q + lane/8, column lane%8); items are dealt round-robin to the four warps of a quadrant =================
         mbar_wait(acc_bar, 0);
         tc_fence_after();
+        pdl_trigger();
         if (tid == 0) WIN_STAMP(5);
         const int q = warp & 3;
         const int lr = 4 * q + (lane >> 3), lc = lane & 7;
@@ -380,6 +382,8 @@ struct PackArgs {
     int kc1, np1, kc2, np2, kcd, npd;
 };
 __global__ void __launch_bounds__(256) win_pack_kernel(PackArgs a) {
+    pdl_wait();
+    pdl_trigger();
     const int n1 = 5 * a.kc1 * a.np1, n2 = 25 * a.kc2 * a.np2, nd = 25 * a.kcd * a.npd;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n1 + n2 + nd; i += gridDim.x * blockDim.x) {
         if (i < n1) {                                   // [ky][kg][oc][4], k = ic*5 + kx
@@ -411,7 +415,7 @@ static int win_launch(const WinArgs& a, cudaStream_t s) {
     }
     WinArgs b = a;
     b.dbg = g_win_dbg;
-    kern<<<(a.B + C::G - 1) / C::G, WIN_THREADS, C::SMEM, s>>>(b);
+    B200DP_CHECK(launch_pdl(kern, dim3((a.B + C::G - 1) / C::G), dim3(WIN_THREADS), C::SMEM, s, b));
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }
@@ -452,7 +456,7 @@ extern "C" int b200dp_tcw_pack_weights(const float* w1, const float* w2, float* 
     B200DP_REQUIRE(pack_layout(d, L), "unsupported (in_ch, c1, c2): expected (1,6,16) or (3,24,64)");
     PackArgs a{w1, w2, wpack + L.o1, wpack + L.o2, wpack + L.od, d.in_ch, d.c1, d.c2, L.kc1, L.np1, L.kc2, L.np2, L.kcd, L.npd};
     const int grid = (int)((L.total + 255) / 256);
-    win_pack_kernel<<<grid < 296 ? grid : 296, 256, 0, (cudaStream_t)s>>>(a);
+    B200DP_CHECK(launch_pdl(win_pack_kernel, dim3(grid < 296 ? grid : 296), dim3(256), 0, (cudaStream_t)s, a));
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }
