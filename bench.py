@@ -200,7 +200,9 @@ def run_own(args):
             "ms_per_step": ms / K, "higher_is_better": True,
             "scaling": "strong" if args.config == "strong4096" else "weak",
             "vs_baseline": None,
-            "dtype": "tf32 tensor-core GEMMs (fp32 storage/accumulate), fp32 convs" if stepper.dtype == "tf32" else "fp32",
+            "dtype": ("fp32" if stepper.dtype == "fp32" else
+                      "tf32 tcgen05 GEMMs" + (" + tf32 tcgen05 conv fprop/dgrad + bf16 tcgen05 conv wgrad" if stepper.net.conv_tc
+                                              else " + fp32 CUDA-core convs") + " (fp32 storage, accumulation and master weights)"),
             "data": "synthetic", "impl": "b200dp",
             "config": {"model": "cnn.py LeNet" if args.config != "wide_cifar" else "cnn.py LeNet 4x wide, CIFAR-shaped",
                        "global_batch": batch * world, "per_gpu_batch": batch, "seq_len": None,
