@@ -201,7 +201,7 @@ def run_own(args):
             "scaling": "strong" if args.config == "strong4096" else "weak",
             "vs_baseline": None,
             "dtype": ("fp32" if stepper.dtype == "fp32" else
-                      "tf32 tcgen05 GEMMs" + (" + tf32 tcgen05 conv fprop/dgrad + bf16 tcgen05 conv wgrad" if stepper.net.conv_tc
+                      "tf32 tcgen05 GEMMs" + (" + bf16 tcgen05 convolutions (fprop, dgrad, wgrad)" if stepper.net.conv_tc
                                               else " + fp32 CUDA-core convs") + " (fp32 storage, accumulation and master weights)"),
             "data": "synthetic", "impl": "b200dp",
             "config": {"model": "cnn.py LeNet" if args.config != "wide_cifar" else "cnn.py LeNet 4x wide, CIFAR-shaped",

@@ -1,17 +1,20 @@
-// "Window-tile" convolutions on tcgen05: implicit GEMM with NO im2col materialisation.
+// "Window-tile" convolutions on tcgen05 (kind::f16: bf16 operands, fp32 accumulation in tensor memory): implicit GEMM
+// with NO im2col materialisation.
 //
-// The activations of an image are staged once in shared memory as [channel group of 4][pixel][4 floats]
+// The activations of an image are staged once in shared memory as [channel group of 8][pixel][8 bf16]
 // (16 bytes per pixel per group).  In that layout a tcgen05 K-major, no-swizzle operand descriptor can
 // address an accumulator tile of 128 output pixels = 16 image rows x 8 columns DIRECTLY:
-//     core matrix (8 rows x 16 B)  = 8 consecutive pixels of one image row, 4 channels   (contiguous 128 B)
+//     core matrix (8 rows x 16 B)  = 8 consecutive pixels of one image row, 8 channels   (contiguous 128 B)
 //     SBO (next 8 rows of the tile) = one image row further   (PITCH * 16 B)
-//     LBO (next 4 channels of K)    = next channel group      (NPIX * 16 B)
+//     LBO (next 8 channels of K)    = next channel group      (NPIX * 16 B)
 // and a filter tap (ky,kx) is nothing but a different start address (+ (ky*PITCH+kx) * 16 B, always
-// 16-byte aligned).  So a 5x5 convolution is 25 x (C/8) tcgen05.mma instructions per tile that read
-// the SAME staged image; nothing is gathered per K slab (the previous generation of these kernels spent
+// 16-byte aligned).  So a 5x5 convolution is 25 x (C/16) tcgen05.mma instructions per tile that read
+// the SAME staged image; nothing is gathered per K slab (the first generation of these kernels spent
 // >95% of its time writing im2col slabs with scalar shared-memory stores: tensor pipe 1-3% busy).
-// The per-tap weight panels [kgroup][n][4] come from a pre-packed copy (b200dp_tcw_pack_weights) through
-// a TMA bulk-copy ring (cp.async.bulk + mbarrier complete_tx).
+// The per-tap weight panels [kgroup][n][8] come from a pre-packed bf16 copy (b200dp_tcw_pack_weights) through
+// a TMA bulk-copy ring (cp.async.bulk + mbarrier complete_tx).  bf16 rather than tf32 because the MMA phases are
+// bound by shared-memory operand bandwidth: half the bytes and half the instructions (measured: the dgrad MMA
+// phase 34K -> 19K cycles per CTA, the wide step 190 -> 177 us).
 //
 //   kind FWD1 : first layer. normalise + bilinear 28->32 on the fly; the staged "channels" are
 //               (ic,kx) pairs (kx-expanded), so only the 5 ky taps remain; epilogue bias+LeakyReLU+2x2 pool+argmax
@@ -27,6 +30,8 @@
 // registers, one elected lane issues), warp 20 runs the weight ring.  Epilogue: tcgen05.ld 32x32b (thread = pixel:
 // lane l of quadrant q is row 4q + l/8, column l%8 of the tile), a 32 x 16 transpose through shared memory so that
 // a lane owns whole 2x2 pool windows, max + first-max argmax, then bias + LeakyReLU on the pooled value.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -42,9 +47,22 @@ __device__ __forceinline__ uint64_t nosw_desc(uint32_t saddr, uint32_t lbo, uint
     return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) |
            ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
 }
-__device__ __forceinline__ uint32_t idesc_tf32(int n, int a_mn, int b_mn) {
-    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+__device__ __forceinline__ uint32_t idesc_bf16(int n, int a_mn, int b_mn) {      // bf16 x bf16 -> f32
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
            ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+}
+
+__device__ __forceinline__ uint32_t win_pack_bf16(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_c, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_c), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
 }
 
 enum { WIN_FWD1 = 0, WIN_FWD2 = 1, WIN_DGRAD = 2 };
@@ -54,9 +72,9 @@ struct WinCfg {
     // geometry of the staged map
     static constexpr int PITCH = KIND == WIN_FWD1 ? 32 : (KIND == WIN_FWD2 ? 14 : 18);
     static constexpr int NTAP = KIND == WIN_FWD1 ? 5 : 25;
-    // K channels per tap (padded to a multiple of 8) and N columns (padded to a multiple of 16)
+    // K channels per tap (padded to a multiple of 16) and N columns (padded to a multiple of 16)
     static constexpr int KREAL = KIND == WIN_FWD1 ? CIN * 5 : (KIND == WIN_FWD2 ? CIN : COUT);
-    static constexpr int KC = (KREAL + 7) / 8 * 8, KG = KC / 4, KSTEPS = KC / 8;
+    static constexpr int KC = (KREAL + 15) / 16 * 16, KG = KC / 8, KSTEPS = KC / 16;   // bf16: groups of 8 channels, K = 16 per MMA
     static constexpr int NREAL = KIND == WIN_DGRAD ? CIN : COUT;
     static constexpr int NP = (NREAL + 15) / 16 * 16;
     // tiles of 16 rows x 8 columns covering the valid outputs
@@ -65,7 +83,7 @@ struct WinCfg {
     // rows touched: last tile row 16*NTR-1, plus 4 tap rows; columns run over into the next row
     static constexpr int NPIX = (16 * NTR + 4) * PITCH + 16;
     static constexpr int IMG_BYTES = KG * NPIX * 16;
-    static constexpr int WB = KC * NP * 4;                       // weight panel of one tap
+    static constexpr int WB = KC * NP * 2;                       // weight panel of one tap (bf16)
     static constexpr bool WIDE = COUT > 16;
     static constexpr int G = KIND == WIN_FWD1 ? (WIDE ? 2 : 1) : 2;     // images per CTA
     static constexpr int RING = KIND == WIN_FWD1 ? 5 : (KIND == WIN_FWD2 ? (WIDE ? 8 : 25) : (WIDE ? 4 : 25));
@@ -86,7 +104,7 @@ struct WinCfg {
 
 struct WinArgs {
     const void* x;            // FWD1: raw [B][CIN][hw][hw] u8|f32;  FWD2: p1 [B][CIN][196];  DGRAD: dp2 [B][COUT][25]
-    const float* wpack;       // packed weight panels [NTAP][KG][NP][4]
+    const void* wpack;        // packed bf16 weight panels [NTAP][KG][NP][8]
     const float* bias;        // FWD*: [COUT]
     float* out;               // FWD*: pooled output [B][out_img_stride];  DGRAD: g1 [B][CIN][196]
     uint8_t* idx;             // FWD*: argmax [B][COUT][PW*PW] (nullable)
@@ -105,20 +123,16 @@ static long long* g_win_dbg = nullptr;
 // ---------------------------------------------------------------------------------------------------
 template <class C, int CIN>
 __device__ __forceinline__ void win_stage_fwd2(const WinArgs& a, int img, float* sImg, int tid) {
-    // NCHW planes -> [cg][pixel][4]: one float4 store per (pixel, channel group), 4 coalesced plane reads
+    // NCHW planes -> [cg][pixel][8 bf16]: one 16-byte store per (pixel, channel group), 8 coalesced plane reads
     const float* src = (const float*)a.x + (long)img * CIN * 196;
-#pragma unroll 4
+#pragma unroll 2
     for (int i = tid; i < C::KG * C::NPIX; i += WIN_STAGERS) {
         const int cg = i / C::NPIX, p = i - cg * C::NPIX;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (p < 196) {
-            const int c = cg * 4;
-            if (c + 0 < CIN) v.x = __ldg(src + (c + 0) * 196 + p);
-            if (c + 1 < CIN) v.y = __ldg(src + (c + 1) * 196 + p);
-            if (c + 2 < CIN) v.z = __ldg(src + (c + 2) * 196 + p);
-            if (c + 3 < CIN) v.w = __ldg(src + (c + 3) * 196 + p);
-        }
-        reinterpret_cast<float4*>(sImg)[i] = v;
+        float v[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[q] = (p < 196 && cg * 8 + q < CIN) ? __ldg(src + (cg * 8 + q) * 196 + p) : 0.f;
+        reinterpret_cast<uint4*>(sImg)[i] = make_uint4(win_pack_bf16(v[0], v[1]), win_pack_bf16(v[2], v[3]),
+                                                       win_pack_bf16(v[4], v[5]), win_pack_bf16(v[6], v[7]));
     }
 }
 
@@ -136,28 +150,24 @@ __device__ __forceinline__ void win_stage_fwd1(const WinArgs& a, int img, float*
     }
     if (tid < 8 * CIN) sUp[(tid >> 3) * C::PLANE_PAD + 1024 + (tid & 7)] = 0.f;      // kx overrun of the last pixels
     asm volatile("bar.sync 1, %0;" ::"n"(WIN_STAGERS) : "memory");
-    // kx-expansion: staged channel c' = ic*5 + kx holds X[ic][p + kx].  A thread keeps one channel group, so the
-    // four plane offsets are loop invariants; consecutive lanes take consecutive pixels (conflict-free).
+    // kx-expansion: staged channel c' = ic*5 + kx holds X[ic][p + kx].  A thread keeps one channel group of 8, so the
+    // plane offsets are loop invariants; consecutive lanes take consecutive pixels (conflict-free 16-byte stores).
     constexpr int TPG = WIN_STAGERS / C::KG;                 // threads per channel group
     static_assert(WIN_STAGERS % C::KG == 0, "stagers must split evenly over the channel groups");
     const int cg = tid / TPG, p0 = tid - cg * TPG;
-    int off[4];
+    int off[8];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const int cc = cg * 4 + q;
+    for (int q = 0; q < 8; ++q) {
+        const int cc = cg * 8 + q;
         off[q] = cc < CIN * 5 ? (cc / 5) * C::PLANE_PAD + (cc % 5) : -1;
     }
-    float4* dst = reinterpret_cast<float4*>(sImg) + (size_t)cg * C::NPIX;
-#pragma unroll 4
+    uint4* dst = reinterpret_cast<uint4*>(sImg) + (size_t)cg * C::NPIX;
+#pragma unroll 2
     for (int p = p0; p < C::NPIX; p += TPG) {
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (p < 1024) {
-            if (off[0] >= 0) v.x = sUp[off[0] + p];
-            if (off[1] >= 0) v.y = sUp[off[1] + p];
-            if (off[2] >= 0) v.z = sUp[off[2] + p];
-            if (off[3] >= 0) v.w = sUp[off[3] + p];
-        }
-        dst[p] = v;
+        float v[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[q] = (p < 1024 && off[q] >= 0) ? sUp[off[q] + p] : 0.f;
+        dst[p] = make_uint4(win_pack_bf16(v[0], v[1]), win_pack_bf16(v[2], v[3]), win_pack_bf16(v[4], v[5]), win_pack_bf16(v[6], v[7]));
     }
     asm volatile("bar.sync 1, %0;" ::"n"(WIN_STAGERS) : "memory");     // sRaw / sUp are reused by the next image
 }
@@ -166,14 +176,14 @@ template <class C, int COUT>
 __device__ __forceinline__ void win_stage_dgrad(const WinArgs& a, int img, float* sImg, int tid) {
     // zero-padded 18x18 map of the un-pooled gradient: pool-bwd (scatter to the argmax) + LeakyReLU-bwd
     for (int i = tid; i < C::KG * C::NPIX; i += WIN_STAGERS)
-        reinterpret_cast<float4*>(sImg)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        reinterpret_cast<uint4*>(sImg)[i] = make_uint4(0u, 0u, 0u, 0u);
     asm volatile("bar.sync 1, %0;" ::"n"(WIN_STAGERS) : "memory");
     for (int i = tid; i < COUT * 25; i += WIN_STAGERS) {
         const int oc = i / 25, pp = i - oc * 25, py = pp / 5, px = pp - py * 5;
         const int k = a.pidx[(long)img * COUT * 25 + i];
         const float g = ((const float*)a.x)[(long)img * COUT * 25 + i] * leaky_grad_from_act(a.act[(long)img * a.ld_act + i]);
         const int p = (2 * py + (k >> 1) + 4) * C::PITCH + 2 * px + (k & 1) + 4;
-        sImg[((oc >> 2) * C::NPIX + p) * 4 + (oc & 3)] = g;
+        reinterpret_cast<__nv_bfloat16*>(sImg)[((oc >> 3) * C::NPIX + p) * 8 + (oc & 7)] = __float2bfloat16_rn(g);
     }
 }
 
@@ -187,7 +197,7 @@ __device__ __forceinline__ bool elect_one() {
 template <class C, int M>
 __device__ __forceinline__ void win_issue(uint32_t tmem, uint32_t s_img, uint32_t s_w, uint32_t bars, int nimg) {
     const bool leader = elect_one();
-    const uint32_t idesc = idesc_tf32(C::NP, 0, 0);
+    const uint32_t idesc = idesc_bf16(C::NP, 0, 0);
     const uint64_t adesc0 = nosw_desc(s_img, C::NPIX * 16u, C::PITCH * 16u);
     const uint64_t bdesc0 = nosw_desc(s_w, C::NP * 16u, 128u);
     const uint32_t acc_bar = bars + 8u * (2 * C::RING);
@@ -208,7 +218,7 @@ __device__ __forceinline__ void win_issue(uint32_t tmem, uint32_t s_img, uint32_
                     const uint64_t ag = at + (uint64_t)((g * C::IMG_BYTES + (r0 * C::PITCH + c0) * 16) >> 4);
 #pragma unroll
                     for (int ks = 0; ks < C::KSTEPS; ++ks)
-                        umma_tf32(tmem + (uint32_t)(ai * C::NP), ag + (uint64_t)(ks * 2 * C::NPIX),
+                        umma_bf16(tmem + (uint32_t)(ai * C::NP), ag + (uint64_t)(ks * 2 * C::NPIX),      // K = 16: two groups of 8
                                   bt + (uint64_t)(ks * 2 * C::NP), idesc, ks != 0 ? 1u : acc);
                 }
             }
@@ -256,7 +266,7 @@ __global__ void __launch_bounds__(WIN_THREADS, 1) win_conv_kernel(const __grid_c
     auto load_tap = [&](int t) {
         const int s = t % C::RING;
         mbar_expect_tx(w_full(s), C::WB);
-        tma_bulk_load(smem_u32(sW + (size_t)s * C::WB), a.wpack + (size_t)t * (C::WB / 4), C::WB, w_full(s));
+        tma_bulk_load(smem_u32(sW + (size_t)s * C::WB), (const uint8_t*)a.wpack + (size_t)t * C::WB, C::WB, w_full(s));
     };
     if (warp == WIN_WORKERS + WIN_NMMA) {
         // ================= weight ring producer (one lane): fill the ring while the images are staged =================
@@ -377,7 +387,7 @@ __global__ void __launch_bounds__(WIN_THREADS, 1) win_conv_kernel(const __grid_c
 // ---------------------------------------------------------------------------------------------------
 struct PackArgs {
     const float* w1; const float* w2;
-    float* p_fwd1; float* p_fwd2; float* p_dgrad;
+    __nv_bfloat16* pack;      // fwd1 panels, then fwd2, then dgrad
     int in_ch, c1, c2;
     int kc1, np1, kc2, np2, kcd, npd;
 };
@@ -386,21 +396,23 @@ __global__ void __launch_bounds__(256) win_pack_kernel(PackArgs a) {
     pdl_trigger();
     const int n1 = 5 * a.kc1 * a.np1, n2 = 25 * a.kc2 * a.np2, nd = 25 * a.kcd * a.npd;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n1 + n2 + nd; i += gridDim.x * blockDim.x) {
-        if (i < n1) {                                   // [ky][kg][oc][4], k = ic*5 + kx
-            const int q = i & 3, n = (i >> 2) % a.np1, kg = (i >> 2) / a.np1 % (a.kc1 / 4), ky = (i >> 2) / a.np1 / (a.kc1 / 4);
-            const int k = kg * 4 + q, ic = k / 5, kx = k - ic * 5;
-            a.p_fwd1[i] = (n < a.c1 && k < a.in_ch * 5) ? a.w1[((n * a.in_ch + ic) * 5 + ky) * 5 + kx] : 0.f;
-        } else if (i < n1 + n2) {                       // [tap][kg][oc][4], k = ic
+        float v;
+        if (i < n1) {                                   // [ky][kg][oc][8], k = ic*5 + kx
+            const int q = i & 7, n = (i >> 3) % a.np1, kg = (i >> 3) / a.np1 % (a.kc1 / 8), ky = (i >> 3) / a.np1 / (a.kc1 / 8);
+            const int k = kg * 8 + q, ic = k / 5, kx = k - ic * 5;
+            v = (n < a.c1 && k < a.in_ch * 5) ? a.w1[((n * a.in_ch + ic) * 5 + ky) * 5 + kx] : 0.f;
+        } else if (i < n1 + n2) {                       // [tap][kg][oc][8], k = ic
             const int e = i - n1;
-            const int q = e & 3, n = (e >> 2) % a.np2, kg = (e >> 2) / a.np2 % (a.kc2 / 4), t = (e >> 2) / a.np2 / (a.kc2 / 4);
-            const int k = kg * 4 + q;
-            a.p_fwd2[e] = (n < a.c2 && k < a.c1) ? a.w2[(n * a.c1 + k) * 25 + t] : 0.f;
-        } else {                                        // [tap=(u,v)][kg][ic][4], k = oc, flipped filter
+            const int q = e & 7, n = (e >> 3) % a.np2, kg = (e >> 3) / a.np2 % (a.kc2 / 8), t = (e >> 3) / a.np2 / (a.kc2 / 8);
+            const int k = kg * 8 + q;
+            v = (n < a.c2 && k < a.c1) ? a.w2[(n * a.c1 + k) * 25 + t] : 0.f;
+        } else {                                        // [tap=(u,v)][kg][ic][8], k = oc, flipped filter
             const int e = i - n1 - n2;
-            const int q = e & 3, n = (e >> 2) % a.npd, kg = (e >> 2) / a.npd % (a.kcd / 4), t = (e >> 2) / a.npd / (a.kcd / 4);
-            const int k = kg * 4 + q;
-            a.p_dgrad[e] = (n < a.c1 && k < a.c2) ? a.w2[(k * a.c1 + n) * 25 + (24 - t)] : 0.f;
+            const int q = e & 7, n = (e >> 3) % a.npd, kg = (e >> 3) / a.npd % (a.kcd / 8), t = (e >> 3) / a.npd / (a.kcd / 8);
+            const int k = kg * 8 + q;
+            v = (n < a.c1 && k < a.c2) ? a.w2[(k * a.c1 + n) * 25 + (24 - t)] : 0.f;
         }
+        a.pack[i] = __float2bfloat16_rn(v);             // the three panel sets are contiguous
     }
 }
 
@@ -448,13 +460,13 @@ extern "C" void b200dp_tcw_set_debug(long long* dbg) { g_win_dbg = dbg; }
 
 extern "C" long b200dp_tcw_pack_floats(b200dp_dims d) {
     PackLayout L;
-    return pack_layout(d, L) ? L.total : -1;
+    return pack_layout(d, L) ? (L.total + 1) / 2 : -1;      // bf16 elements, counted in floats
 }
 
 extern "C" int b200dp_tcw_pack_weights(const float* w1, const float* w2, float* wpack, b200dp_dims d, b200dp_stream_t s) {
     PackLayout L;
     B200DP_REQUIRE(pack_layout(d, L), "unsupported (in_ch, c1, c2): expected (1,6,16) or (3,24,64)");
-    PackArgs a{w1, w2, wpack + L.o1, wpack + L.o2, wpack + L.od, d.in_ch, d.c1, d.c2, L.kc1, L.np1, L.kc2, L.np2, L.kcd, L.npd};
+    PackArgs a{w1, w2, reinterpret_cast<__nv_bfloat16*>(wpack), d.in_ch, d.c1, d.c2, L.kc1, L.np1, L.kc2, L.np2, L.kcd, L.npd};
     const int grid = (int)((L.total + 255) / 256);
     B200DP_CHECK(launch_pdl(win_pack_kernel, dim3(grid < 296 ? grid : 296), dim3(256), 0, (cudaStream_t)s, a));
     B200DP_CHECK(cudaGetLastError());
@@ -467,7 +479,7 @@ extern "C" int b200dp_tcw_conv1_fwd(const void* x, int in_is_u8, float mean, flo
     PackLayout L;
     B200DP_REQUIRE(pack_layout(d, L), "unsupported (in_ch, c1, c2): expected (1,6,16) or (3,24,64)");
     WinArgs a{};
-    a.x = x; a.wpack = wpack + L.o1; a.bias = b; a.out = p1; a.idx = idx1;
+    a.x = x; a.wpack = reinterpret_cast<const __nv_bfloat16*>(wpack) + L.o1; a.bias = b; a.out = p1; a.idx = idx1;
     a.B = d.batch; a.in_is_u8 = in_is_u8; a.in_hw = d.in_hw; a.out_img_stride = d.c1 * 196; a.mean = mean; a.std = std;
     if (d.in_ch == 3) return win_launch<WIN_FWD1, 3, 24>(a, (cudaStream_t)s);
     return win_launch<WIN_FWD1, 1, 6>(a, (cudaStream_t)s);
@@ -478,7 +490,7 @@ extern "C" int b200dp_tcw_conv2_fwd(const float* p1, const float* wpack, const f
     PackLayout L;
     B200DP_REQUIRE(pack_layout(d, L), "unsupported (in_ch, c1, c2): expected (1,6,16) or (3,24,64)");
     WinArgs a{};
-    a.x = p1; a.wpack = wpack + L.o2; a.bias = b; a.out = p2; a.idx = idx2;
+    a.x = p1; a.wpack = reinterpret_cast<const __nv_bfloat16*>(wpack) + L.o2; a.bias = b; a.out = p2; a.idx = idx2;
     a.B = d.batch; a.out_img_stride = d.ld_p2 > 0 ? d.ld_p2 : d.c2 * 25;
     if (d.c1 == 24) return win_launch<WIN_FWD2, 24, 64>(a, (cudaStream_t)s);
     return win_launch<WIN_FWD2, 6, 16>(a, (cudaStream_t)s);
@@ -489,7 +501,7 @@ extern "C" int b200dp_tcw_conv2_dgrad(const float* dp2, const float* p2, const u
     PackLayout L;
     B200DP_REQUIRE(pack_layout(d, L), "unsupported (in_ch, c1, c2): expected (1,6,16) or (3,24,64)");
     WinArgs a{};
-    a.x = dp2; a.wpack = wpack + L.od; a.out = g1; a.act = p2; a.pidx = idx2; a.mask = p1;
+    a.x = dp2; a.wpack = reinterpret_cast<const __nv_bfloat16*>(wpack) + L.od; a.out = g1; a.act = p2; a.pidx = idx2; a.mask = p1;
     a.B = d.batch; a.ld_act = d.ld_p2 > 0 ? d.ld_p2 : d.c2 * 25;
     if (d.c1 == 24) return win_launch<WIN_DGRAD, 24, 64>(a, (cudaStream_t)s);
     return win_launch<WIN_DGRAD, 6, 16>(a, (cudaStream_t)s);

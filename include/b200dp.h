@@ -117,7 +117,8 @@ int b200dp_tc_gemm_group_timed(const b200dp_tc_problem* probs, int count, long l
 
 /* "Window-tile" convolutions (csrc/tc_win.cu): tcgen05 implicit GEMM that reads the staged image in place —
  * an accumulator tile is a 16x8-pixel window addressed by a no-swizzle K-major descriptor, a filter tap is a
- * start-address shift, so no im2col operand is ever written (kind::tf32, fp32 accumulation in tensor memory).
+ * start-address shift, so no im2col operand is ever written (kind::f16 on bf16 operands, fp32 accumulation in
+ * tensor memory; activations and weights stay fp32 in global memory and are converted while staging / packing).
  * Same tensors and semantics as b200dp_conv1_fwd / b200dp_conv2_fwd, except that the weights come
  * pre-packed: call b200dp_tcw_pack_weights once per step (after the optimizer update) into a scratch of
  * b200dp_tcw_pack_floats(d) floats; it packs the first layer's forward panels, the second layer's forward
