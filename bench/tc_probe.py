@@ -41,6 +41,11 @@ for (M, N, K, amn, bmn) in [(256, 120, 400, False, False), (256, 480, 1600, Fals
     e1.record()
     torch.cuda.synchronize()
     t_plain = e0.elapsed_time(e1) * 100
+    lib.b200dp_tc_gemm_set_debug.argtypes = [C.c_void_p]; lib.b200dp_tc_gemm_set_debug.restype = None
+    dbg2 = torch.zeros(32, dtype=torch.int64, device=dev)
+    lib.b200dp_tc_gemm_set_debug(dbg2.data_ptr()); split_call(); torch.cuda.synchronize(); lib.b200dp_tc_gemm_set_debug(None)
+    u = dbg2.tolist()
+    print(f"   split/retiled CTA 0: setup {u[1]-u[0]} acc_done {u[2]-u[0]} staged {u[5]-u[0]} epi_done {u[3]-u[0]} end {u[4]-u[0]} landed {[x-u[0] for x in u[16:24] if x]}")
     print(f"   back-to-back x10: plain {t_plain:.1f} us/launch, split-K {t_split:.1f} us/launch (ws floats {ws.ws.numel()})")
     t = dbg.tolist()
     t0 = t[0]

@@ -190,10 +190,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     } else {
         // ================= epilogue (warps 2..9): warp reads TMEM lane quarter warp%4, column half (warp-2)/4.
         // tcgen05.ld gives a thread 16 columns of ITS row; storing those directly costs one L1 wavefront per
-        // element (32 lanes -> 32 different lines; measured: 16 K cycles for a 128x128 tile, the whole epilogue).
-        // So the warp's 32 x half sub-tile is transposed through shared memory (the operand ring is idle now) and
-        // written with lane = column: one 128-byte wavefront per row.  The row loop is unrolled so the loads of
-        // several rows are in flight (a lone warp per scheduler pays the full latency of every dependent step). =====
+        // element (32 lanes -> 32 different lines; measured: 16 K cycles for a 128x128 tile).  So the warp's 32 x half
+        // sub-tile is transposed through shared memory (the operand ring is idle now) and handled with
+        // lane = (row group, 4 consecutive columns): 16-byte shared loads, 16-byte coalesced global accesses, and
+        // only half/4 iterations per warp (a lone warp per scheduler pays ~5 cycles per dependent instruction,
+        // so the instruction count is what matters). =====
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
         if (threadIdx.x == 64) TC_STAMP(2);          // accumulator complete
@@ -202,7 +203,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
         const int h = (warp - 2) >> 2;
         const int half = P.bn >> 1, c_lo = h * half;          // this warp's columns [c_lo, c_lo + half) of the tile
         const int n_out = P.colext ? P.N - 1 : P.N;
-        constexpr int TP = TC_BN_MAX / 2 + 1;                  // odd pitch: row-wise writes and column-wise reads conflict-free
+        constexpr int TP = TC_BN_MAX / 2 + 4;                  // 68 floats: 16-byte aligned rows, conflict-free 128-bit accesses
         float* sT = reinterpret_cast<float*>(smem_raw + (base - smem_u32(smem_raw))) + (warp - 2) * 32 * TP;
         const int ncols = max(0, min(half, P.N - n0 - c_lo));  // warp-uniform
 #pragma unroll 1
@@ -210,59 +211,70 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
             uint32_t r[16];
             tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c_lo + c * 16), r);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) sT[lane * TP + c * 16 + j] = __uint_as_float(r[j]);
+            for (int j = 0; j < 16; j += 4)
+                *reinterpret_cast<uint4*>(sT + lane * TP + c * 16 + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
         }
         __syncwarp();
         if (threadIdx.x == 64) TC_STAMP(5);
         const int rows = max(0, min(32, P.M - (m0 + q * 32)));    // warp-uniform
-        const int nchunk = (ncols + 31) >> 5;                      // 0..2 column chunks of 32 (lane = column)
-        const int mrow0 = m0 + q * 32, ncol0 = n0 + c_lo + lane;
-        float bias_r[2];
-#pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-            const int n = ncol0 + cc * 32;
-            bias_r[cc] = (P.bias && cc < nchunk && cc * 32 + lane < ncols && n < n_out) ? __ldg(P.bias + n) : 0.f;
+        const int vpr = half >> 2;                                 // float4 per row of the sub-tile: 4 / 8 / 16
+        const int rpi = 32 / vpr;                                  // rows covered by one warp-wide access: 8 / 4 / 2
+        const int c4 = (lane % vpr) * 4, r_in = lane / vpr;        // this lane's columns / row inside an iteration
+        const int mrow0 = m0 + q * 32, ncol = n0 + c_lo + c4;
+        const bool col_ok = c4 < ncols;
+        const bool vec_ok = col_ok && c4 + 3 < ncols && ncol + 3 < n_out && ((P.ld_out & 3) == 0) &&
+                            ((reinterpret_cast<uintptr_t>(P.out) & 15) == 0) &&
+                            (!P.mask || (((P.ld_mask & 3) == 0) && ((reinterpret_cast<uintptr_t>(P.mask) & 15) == 0)));
+        float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (P.bias && col_ok) {
+            if (ncol + 0 < n_out) bias4.x = __ldg(P.bias + ncol + 0);
+            if (ncol + 1 < n_out) bias4.y = __ldg(P.bias + ncol + 1);
+            if (ncol + 2 < n_out) bias4.z = __ldg(P.bias + ncol + 2);
+            if (ncol + 3 < n_out) bias4.w = __ldg(P.bias + ncol + 3);
         }
-        auto finish = [&](int rr, int cc, float v) {      // fused epilogue of one element (lane = column)
-            const int m = mrow0 + rr, n = ncol0 + cc * 32;
-            if (n < n_out) {
-                v += cc == 0 ? bias_r[0] : bias_r[1];
-                if (P.act == 1) v = leaky(v);
-                if (P.mask) v *= leaky_grad_from_act(P.mask[(long)m * P.ld_mask + n]);
-                P.out[(long)m * P.ld_out + n] = v;
+        auto finish4 = [&](int rr, float4 v) {            // fused epilogue of 4 consecutive columns of row rr
+            const int m = mrow0 + rr;
+            if (vec_ok) {
+                v.x += bias4.x; v.y += bias4.y; v.z += bias4.z; v.w += bias4.w;
+                if (P.act == 1) { v.x = leaky(v.x); v.y = leaky(v.y); v.z = leaky(v.z); v.w = leaky(v.w); }
+                if (P.mask) {
+                    const float4 k = *reinterpret_cast<const float4*>(P.mask + (long)m * P.ld_mask + ncol);
+                    v.x *= leaky_grad_from_act(k.x); v.y *= leaky_grad_from_act(k.y);
+                    v.z *= leaky_grad_from_act(k.z); v.w *= leaky_grad_from_act(k.w);
+                }
+                *reinterpret_cast<float4*>(P.out + (long)m * P.ld_out + ncol) = v;
             } else {
-                P.colext[m] = v;
-            }
-        };
-
-        // coalesced output of the staged sub-tile: fully unrolled (compile-time trip counts) so that the shared-memory
-        // reads, mask loads and stores of all rows are independent instructions in flight together
-        auto write_out = [&]() {
+                const float e[4] = {v.x, v.y, v.z, v.w}, bb[4] = {bias4.x, bias4.y, bias4.z, bias4.w};
 #pragma unroll
-            for (int cc = 0; cc < 2; ++cc) {
-                if (cc < nchunk && cc * 32 + lane < ncols) {
-#pragma unroll
-                    for (int rr = 0; rr < 32; ++rr)
-                        if (rr < rows) finish(rr, cc, sT[rr * TP + cc * 32 + lane]);
+                for (int j = 0; j < 4; ++j) {
+                    const int n = ncol + j;
+                    if (c4 + j < ncols && n < P.N) {
+                        float x = e[j];
+                        if (n < n_out) {
+                            x += bb[j];
+                            if (P.act == 1) x = leaky(x);
+                            if (P.mask) x *= leaky_grad_from_act(P.mask[(long)m * P.ld_mask + n]);
+                            P.out[(long)m * P.ld_out + n] = x;
+                        } else {
+                            P.colext[m] = x;
+                        }
+                    }
                 }
             }
         };
 
         if (P.splits == 1) {
-            write_out();
+#pragma unroll 4
+            for (int rr = r_in; rr < rows; rr += rpi)
+                if (col_ok) finish4(rr, *reinterpret_cast<const float4*>(sT + rr * TP + c4));
         } else {
-            // ---- split-K: park the raw partial tile (thread = row: 16-byte stores into the private workspace),
-            //      take a ticket; the last CTA of the tile sums the partials in split order (deterministic),
-            //      re-stages the sums and runs the same coalesced epilogue ----
+            // ---- split-K: park the raw partial tile ([128][bn], coalesced 16-byte rows), take a ticket; the last CTA of
+            //      the tile sums the partials in split order (deterministic) and runs the epilogue ----
             const long sstride = (long)TC_BM * P.bn;
-            float* wt = P.ws + ((long)tile * P.splits + split) * sstride + (q * 32 + lane) * P.bn + c_lo;
-            for (int c = 0; c * 16 < ncols; ++c) {
-#pragma unroll
-                for (int j = 0; j < 16; j += 4)
-                    *reinterpret_cast<float4*>(wt + c * 16 + j) =
-                        make_float4(sT[lane * TP + c * 16 + j], sT[lane * TP + c * 16 + j + 1], sT[lane * TP + c * 16 + j + 2],
-                                    sT[lane * TP + c * 16 + j + 3]);
-            }
+            float* wt = P.ws + ((long)tile * P.splits + split) * sstride + (q * 32) * P.bn + c_lo + c4;
+#pragma unroll 4
+            for (int rr = r_in; rr < rows; rr += rpi)
+                if (col_ok) *reinterpret_cast<float4*>(wt + rr * P.bn) = *reinterpret_cast<const float4*>(sT + rr * TP + c4);
             __threadfence();
             asm volatile("bar.sync 2, %0;" ::"n"(32 * TC_EPI_WARPS) : "memory");
             if (threadIdx.x == 64) {
@@ -274,36 +286,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
             asm volatile("bar.sync 2, %0;" ::"n"(32 * TC_EPI_WARPS) : "memory");
             if (*s_last) {
                 __threadfence();
-                const float* w0 = P.ws + (long)tile * P.splits * sstride + (q * 32 + lane) * P.bn + c_lo;
-                for (int c = 0; c * 16 < ncols; ++c) {
-                    float4 acc[4];
+                const float* w0 = P.ws + (long)tile * P.splits * sstride + (q * 32) * P.bn + c_lo + c4;
+#pragma unroll 2
+                for (int rr = r_in; rr < rows; rr += rpi) {
+                    if (col_ok) {
+                        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                        for (int sp0 = 0; sp0 < P.splits; sp0 += 4) {        // 4 loads in flight, added in split order
+                            float4 x[4];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    for (int sp0 = 0; sp0 < P.splits; sp0 += 4) {        // 16 loads in flight, added in split order
-                        float4 x[4][4];
+                            for (int d = 0; d < 4; ++d)
+                                x[d] = (sp0 + d < P.splits) ? __ldcg(reinterpret_cast<const float4*>(w0 + (sp0 + d) * sstride + rr * P.bn))
+                                                            : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-                        for (int d = 0; d < 4; ++d)
-#pragma unroll
-                            for (int u = 0; u < 4; ++u)
-                                x[d][u] = (sp0 + d < P.splits)
-                                              ? __ldcg(reinterpret_cast<const float4*>(w0 + (sp0 + d) * sstride + c * 16) + u)
-                                              : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-                        for (int d = 0; d < 4; ++d)
-#pragma unroll
-                            for (int u = 0; u < 4; ++u) {
-                                acc[u].x += x[d][u].x; acc[u].y += x[d][u].y; acc[u].z += x[d][u].z; acc[u].w += x[d][u].w;
-                            }
-                    }
-                    __syncwarp();
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        sT[lane * TP + c * 16 + 4 * u + 0] = acc[u].x; sT[lane * TP + c * 16 + 4 * u + 1] = acc[u].y;
-                        sT[lane * TP + c * 16 + 4 * u + 2] = acc[u].z; sT[lane * TP + c * 16 + 4 * u + 3] = acc[u].w;
+                            for (int d = 0; d < 4; ++d) { acc.x += x[d].x; acc.y += x[d].y; acc.z += x[d].z; acc.w += x[d].w; }
+                        }
+                        finish4(rr, acc);
                     }
                 }
-                __syncwarp();
-                write_out();
             }
         }
     }
@@ -397,6 +396,9 @@ static void tc_plan(const b200dp_tc_problem* probs, int count, bool can_split, T
 
 static int tc_launch(const b200dp_tc_problem* probs, int count, bool retile, float* ws, long ws_floats, unsigned* tickets,
                      int n_tickets, long long* dbg, b200dp_stream_t s);
+static long long* g_tc_dbg = nullptr;
+// Profiling aid: while set, CTA 0 of every tensor-core GEMM launch writes its clock64() stamps to dbg[0..32).
+extern "C" void b200dp_tc_gemm_set_debug(long long* dbg) { g_tc_dbg = dbg; }
 
 extern "C" int b200dp_tc_gemm_group(const b200dp_tc_problem* probs, int count, b200dp_stream_t s) {
     return tc_launch(probs, count, false, nullptr, 0, nullptr, 0, nullptr, s);
@@ -429,7 +431,7 @@ static int tc_launch(const b200dp_tc_problem* probs, int count, bool retile, flo
     TcGroup g;
     memset(&g, 0, sizeof(g));
     g.count = count;
-    g.dbg = dbg;
+    g.dbg = dbg ? dbg : g_tc_dbg;
     int total = 0;
     for (int i = 0; i < count; ++i) {
         const b200dp_tc_problem& q = probs[i];
