@@ -39,9 +39,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--world-size", type=int, default=0, help="ranks to spawn (0 = one per visible GPU)")
     p.add_argument("--cpu", action="store_true", help="run on CPU with gloo instead of exiting when no GPU")
     p.add_argument("--dtype", choices=["auto", "fp32", "tf32", "bf16"], default="auto",
-                   help="fp32 = exact CUDA-core kernels; tf32 = tcgen05 tensor-core GEMMs (fp32 storage and "
-                        "accumulation; bf16 is accepted as an alias); auto = whichever is faster for the model "
-                        "size; master weights are always fp32")
+                   help="fp32 = exact CUDA-core kernels; tf32 / bf16 = the tcgen05 tensor-core path (tf32 dense GEMMs, "
+                        "bf16 convolutions when the model is wide; fp32 storage, accumulation and master weights); "
+                        "auto = whichever is faster for the model size")
     p.add_argument("--optimizer", choices=["adadelta", "sgd", "adam"], default="adadelta")
     p.add_argument("--momentum", type=float, default=0.9)
     p.add_argument("--weight-decay", type=float, default=0.0)

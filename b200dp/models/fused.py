@@ -1,19 +1,24 @@
 """Native LeNet runner: the whole training step as a short fixed sequence of
-hand-written sm_100a kernels over flat arenas, optionally replayed from a CUDA graph.
+hand-written sm_100a kernels over flat arenas, replayed from a CUDA graph.
 
-Step = 9 launches (reference: ~50 ATen/cuDNN/cuBLAS kernels + 10 NCCL all-reduces
-+ 10 divides + the optimizer's elementwise kernels, train.py:45-51):
+Step = 11 launches on the CUDA-core path, 14 on the tensor-core path (reference: ~50 ATen/cuDNN/cuBLAS kernels +
+10 NCCL all-reduces + 10 divides + the optimizer's elementwise kernels, train.py:45-51):
 
-    main stream                                   side stream (overlapped)
-    ---------------------------------------------  -----------------------------
-    conv1 fwd   (normalise+upsample+conv+act+pool)
-    conv2 fwd   (conv+act+pool)
-    conv3 fwd   (GEMM+bias+act)
-    fc1   fwd   (GEMM+bias+act)
+    main stream                                      side stream (overlapped)        tensor-core path
+    -----------------------------------------------  ------------------------------  ------------------------------------
+    (weight pack)                                                                    tcw_pack_weights (bf16 panels)
+    conv1 fwd   (normalise+upsample+conv+act+pool)                                   tcw_conv1_fwd   [tcgen05, bf16]
+    conv2 fwd   (conv+act+pool)                                                      tcw_conv2_fwd   [tcgen05, bf16]
+    conv3 fwd   (GEMM+bias+act)                                                      tc_gemm (split-K) [tcgen05, tf32]
+    fc1   fwd   (GEMM+bias+act)                                                      tc_gemm           [tcgen05, tf32]
     head tail   (fc2+softmax+loss+dlogits+dz1)
-    head bwd A  {dW fc2, dW fc1, dZ3}  ----------> reduce+update bucket 0 (FC.*)
-    head bwd B  {dW conv3, dP2}        ----------> reduce+update bucket 1 (ConvNet.7)
-    conv bwd    (pool/act bwd, dgrad, 2x wgrad) -> reduce+update bucket 2 (ConvNet.1, .4)
+    head bwd A  {dW fc2, dW fc1, dZ3}  ------------> reduce+update bucket 0 (FC.*)   tc_gemm group of 3
+    head bwd B  {dW conv3, dP2}        ------------> reduce+update bucket 1 (conv3)  tc_gemm group of 2
+    conv bwd    (pool/act bwd, dgrad, 2x wgrad) ---> reduce+update bucket 2 (conv)   tcw_conv2_dgrad, tcw_conv_wgrad x2
+
+Which path runs is a measured choice (``dtype="auto"``, ``conv="auto"``): the reference LeNet is a few MFLOP per
+layer and is faster on the fused fp32 CUDA-core kernels; the 4x-wide model runs on the tensor cores.  Every launch
+uses programmatic dependent launch, so the chain's scheduling gaps overlap (csrc/common.cuh).
 
 The reduce+update launch is the fused P2P all-reduce + average + optimizer
 kernel (csrc/reduce_update.cu); with world size 1 it degenerates to the
@@ -44,8 +49,8 @@ class NativeLeNet:
                  spec: ImageSpec = MNIST_SPEC, module: Optional[LeNet] = None, tc: bool = False,
                  conv_tc: Optional[bool] = None):
         """``tc=True`` routes the five GEMM-shaped layers (conv3, FC.0 and their backward, FC.2's weight
-        gradient) through the tcgen05/TMEM/TMA tf32 kernel; ``tc=False`` keeps everything in exact fp32
-        on CUDA cores.  In tc mode the GEMM operand buffers carry one extra column of ones (the bias
+        gradient) through the tcgen05/TMEM/TMA tf32 kernel; ``tc=False`` keeps them in exact fp32 on CUDA cores.
+        ``conv_tc`` does the same for the two 5x5 convolutions (window-tile bf16 tcgen05 kernels).  In tc mode the GEMM operand buffers carry one extra column of ones (the bias
         gradients fall out of the weight-gradient GEMMs) and are padded to a 16-byte row pitch for TMA."""
         native.load()
         self.cfg, self.B, self.device, self.spec = cfg, int(batch), torch.device(device), spec
