@@ -13,6 +13,7 @@
 #include <nvtx3/nvToolsExt.h>
 #include <string.h>
 
+#include <algorithm>
 #include <atomic>
 #include <condition_variable>
 #include <mutex>
@@ -39,17 +40,56 @@ struct Pump {
     bool quit = false, busy = false, failed = false;
     int device = 0;
 
-    void gather(long step) {
+    // ---- gather: the batch rows are split over a small pool (a 788 KB CIFAR batch gathered row by row by one thread
+    // took as long as the GPU step); the helper thread does share 0 and waits for the others ----
+    static constexpr int kWorkers = 3;
+    std::thread workers[kWorkers];
+    std::mutex wmu;
+    std::condition_variable wcv;
+    long job_step = -1;                      // step being gathered (-1: none)
+    unsigned job_seq = 0;                    // bumped per job
+    int job_left = 0;                        // worker shares still running
+    bool wquit = false;
+
+    void gather_rows(long step, int j0, int j1) {
         const int s = (int)(step % d.depth);
         const int64_t* idx = order + step * (long)d.batch;
         uint8_t* hx = (uint8_t*)d.host_x[s];
         int64_t* hy = (int64_t*)d.host_y[s];
         const uint8_t* base = (const uint8_t*)d.images;
         const size_t ib = (size_t)d.image_bytes;
-        for (int j = 0; j < d.batch; ++j) {
+        for (int j = j0; j < j1; ++j) {
             memcpy(hx + (size_t)j * ib, base + (size_t)idx[j] * ib, ib);
             hy[j] = d.targets[idx[j]];
         }
+    }
+    void worker_main(int w) {
+        unsigned seen = 0;
+        std::unique_lock<std::mutex> lk(wmu);
+        for (;;) {
+            wcv.wait(lk, [&] { return wquit || job_seq != seen; });
+            if (wquit) return;
+            seen = job_seq;
+            const long step = job_step;
+            lk.unlock();
+            const int per = (d.batch + kWorkers) / (kWorkers + 1);
+            gather_rows(step, std::min(d.batch, (w + 1) * per), std::min(d.batch, (w + 2) * per));
+            lk.lock();
+            if (--job_left == 0) wcv.notify_all();
+        }
+    }
+    void gather(long step) {
+        const bool split = (size_t)d.batch * (size_t)d.image_bytes >= (256u << 10);   // small batches: not worth a hand-off
+        if (!split) { gather_rows(step, 0, d.batch); return; }
+        {
+            std::lock_guard<std::mutex> lk(wmu);
+            job_step = step; job_left = kWorkers; ++job_seq;
+        }
+        wcv.notify_all();
+        const int per = (d.batch + kWorkers) / (kWorkers + 1);
+        gather_rows(step, 0, std::min(d.batch, per));
+        std::unique_lock<std::mutex> lk(wmu);
+        wcv.wait(lk, [&] { return job_left == 0; });
     }
 
     // Pinned slot j%depth was last read on behalf of step j-depth: by graph j-depth-1 (its prefetch branch),
@@ -106,6 +146,7 @@ extern "C" int b200dp_pump_create(b200dp_pump** out, const b200dp_pump_desc* des
         p->slot_pending[s] = false;
     }
     B200DP_CHECK(cudaEventCreateWithFlags(&p->first_done, cudaEventDisableTiming));
+    for (int w = 0; w < Pump::kWorkers; ++w) p->workers[w] = std::thread([p, w] { p->worker_main(w); });
     p->helper = std::thread([p] { p->helper_main(); });
     *out = (b200dp_pump*)p;
     return 0;
@@ -204,6 +245,13 @@ extern "C" int b200dp_pump_destroy(b200dp_pump* handle) {
     }
     p->cv.notify_all();
     if (p->helper.joinable()) p->helper.join();
+    {
+        std::lock_guard<std::mutex> lk(p->wmu);
+        p->wquit = true;
+    }
+    p->wcv.notify_all();
+    for (int w = 0; w < Pump::kWorkers; ++w)
+        if (p->workers[w].joinable()) p->workers[w].join();
     for (int s = 0; s < p->d.depth; ++s) {
         if (p->slot_pending[s]) cudaEventSynchronize(p->slot_ev[s]);
         cudaEventDestroy(p->slot_ev[s]);
