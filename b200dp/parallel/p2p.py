@@ -113,7 +113,10 @@ class P2PComm:
         return True
 
     # -- per-bucket algorithm choice ---------------------------------------------------
-    OVERLAP_CTAS = 32      # CTAs of a reduce+update that runs while backward kernels still need the SMs
+    OVERLAP_CTAS = 64      # CTAs of a reduce+update that runs beside backward kernels.  Measured on the wide model at 2 GPUs
+                           # (3 MB conv3 bucket; step us / exposed us): 16 CTAs 319 / 153, 32: 237 / 71, 64: 213 / 48,
+                           # 128: 212 / 46, whole GPU: slower again (spinning CTAs hold the SMs backward needs).  The
+                           # buckets are reduced one after the other, so a slow middle bucket delays the last one.
 
     def struct_for(self, bucket_bytes: int, overlapped: bool = False) -> "native.Comm":
         """The ``b200dp_comm`` to pass for a bucket of this size (algorithm chosen per bucket).  ``overlapped``:
