@@ -4,7 +4,7 @@
 // first stage, the host transform of train.py:85.  One launch per stage; the conv output never
 // reaches memory un-pooled.  A thread owns one pooled cell (2x2 conv outputs) for OCT output
 // channels: it keeps the 6x6 input patch in registers and streams weights from shared memory
-// (warp-broadcast reads).  The tcgen05 implicit-GEMM path for the wide model lives in tc_conv.cu.
+// (warp-broadcast reads).  The tcgen05 path for the wide model lives in tc_win.cu / tc_wgrad.cu.
 #include "common.cuh"
 
 namespace b200dp {

@@ -75,18 +75,34 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
-// Byte offset of element (row, k) of a [rows][32 floats] K-major tile in the SWIZZLE_128B layout that
-// tcgen05 expects (16-byte chunk index XOR row%8; tile base 1024-byte aligned).
-__device__ __forceinline__ uint32_t sw128_off(int row, int k) {
-    return (uint32_t)(row * 128 + ((((k >> 2) ^ (row & 7)) << 4) | ((k & 3) << 2)));
+// Operand descriptor WITHOUT swizzle (layout type 0), strides in bytes.  K-major: LBO = next 16-byte chunk along K,
+// SBO = next group of 8 rows.  MN-major: LBO = next group of 8 K rows, SBO = next 16-byte chunk along MN.  The start
+// address only needs 16-byte alignment, which is what lets a filter tap be an address shift (tc_win.cu, tc_wgrad.cu).
+__device__ __forceinline__ uint64_t nosw_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) |
+           ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
 }
-// K-major SWIZZLE_128B shared-memory matrix descriptor (8-row groups 1024 B apart).
-__device__ __forceinline__ uint64_t kmajor_sw128_desc(uint32_t saddr) {
-    return (uint64_t)((saddr & 0x3FFFF) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+// bf16 x bf16 -> f32 instruction descriptor (kind::f16), M = 128; a_mn / b_mn = 1 for MN-major operands.
+__device__ __forceinline__ uint32_t idesc_bf16_m128(int n, int a_mn, int b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+           ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 }
-// tf32 x tf32 -> f32 instruction descriptor, both operands K-major, M = 128.
-__device__ __forceinline__ uint32_t idesc_tf32_m128(int n) {
-    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_c, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_c), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {        // round-to-nearest-even, lo in the low half
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ bool elect_one() {                                 // one lane of a converged warp
+    uint32_t p;
+    asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(p));
+    return p != 0;
 }
 
 }  // namespace b200dp

@@ -33,28 +33,6 @@ constexpr int WG_NSTAGE = 16;                        // stager warps (latency-bo
 constexpr int WG_STAGERS = 32 * WG_NSTAGE;
 constexpr int WG_THREADS = WG_STAGERS + 32;          // + the MMA-issuing warp
 
-__device__ __forceinline__ uint64_t wg_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
-    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) |
-           ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
-}
-__device__ __forceinline__ uint32_t wg_pack_bf16(float lo, float hi) {
-    uint32_t r;
-    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-    return r;
-}
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_c, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_c), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
-}
-__device__ __forceinline__ bool wg_elect() {
-    uint32_t p;
-    asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(p));
-    return p != 0;
-}
-
 template <int LAYER, int CIN, int COUT>
 struct WgCfg {
     static constexpr bool FIRST = LAYER == 1;
@@ -206,8 +184,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wg_conv_kernel(const __grid_con
                 if (p < C::PA) {
                     const float* src = sPl + p0 + p;
                     auto tap = [&](int o) { return o >= 0 ? src[o] : (o == -1 ? 1.f : 0.f); };
-                    sA[(size_t)cg * C::PA + p] = make_uint4(wg_pack_bf16(tap(o0.x), tap(o0.y)), wg_pack_bf16(tap(o0.z), tap(o0.w)),
-                                                            wg_pack_bf16(tap(o1.x), tap(o1.y)), wg_pack_bf16(tap(o1.z), tap(o1.w)));
+                    sA[(size_t)cg * C::PA + p] = make_uint4(pack_bf16x2(tap(o0.x), tap(o0.y)), pack_bf16x2(tap(o0.z), tap(o0.w)),
+                                                            pack_bf16x2(tap(o1.x), tap(o1.y)), pack_bf16x2(tap(o1.z), tap(o1.w)));
                 }
             }
             fence_proxy_async_smem();
@@ -217,9 +195,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wg_conv_kernel(const __grid_con
         if (tid == 0) WG_STAMP(6);                                     // everything staged
     } else {
         // ================= MMA issuer (warp 8): uniform loop, one elected lane =================
-        const bool leader = wg_elect();
-        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
-                               ((uint32_t)(C::NP >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);   // bf16 x bf16 -> f32, A and B MN-major
+        const bool leader = elect_one();
+        const uint32_t idesc = idesc_bf16_m128(C::NP, 1, 1);            // bf16 x bf16 -> f32, A and B MN-major
         for (int ch = 0; ch < nchunks; ++ch) {
             const int b = C::NBUF == 2 ? (ch & 1) : 0;
             mbar_wait(staged(b), (ch / C::NBUF) & 1);
@@ -227,8 +204,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wg_conv_kernel(const __grid_con
             const int ii = ch / C::NCHUNK, ck = ch - ii * C::NCHUNK;
             const uint32_t sa = smem_u32(sAB + (size_t)b * C::A_BYTES);
             const uint32_t sb = smem_u32(sAB + (size_t)C::NBUF * C::A_BYTES + (size_t)(C::NBUF == 2 ? (ii & 1) : 0) * C::B_BYTES);
-            const uint64_t adesc = wg_desc(sa, 128u, C::PA * 16u);      // LBO: next 8 positions; SBO: next channel group
-            const uint64_t bdesc = wg_desc(sb, 128u, C::NPOS * 16u) + (uint64_t)(ck * C::P);
+            const uint64_t adesc = nosw_desc(sa, 128u, C::PA * 16u);      // LBO: next 8 positions; SBO: next channel group
+            const uint64_t bdesc = nosw_desc(sb, 128u, C::NPOS * 16u) + (uint64_t)(ck * C::P);
             if (leader) {
 #pragma unroll 1
                 for (int j = 0; j < C::P / 16; ++j) {           // 16 positions (two 8-row K groups, LBO apart) per MMA

@@ -42,29 +42,6 @@ constexpr int WIN_WORKERS = 16;                      // staging + epilogue warps
 constexpr int WIN_THREADS = 32 * (WIN_WORKERS + WIN_NMMA + 1);
 constexpr int WIN_STAGERS = 32 * 16;
 
-// K-major / MN-major operand descriptor without swizzle (layout type 0), strides in bytes.
-__device__ __forceinline__ uint64_t nosw_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
-    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) |
-           ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
-}
-__device__ __forceinline__ uint32_t idesc_bf16(int n, int a_mn, int b_mn) {      // bf16 x bf16 -> f32
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
-           ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-}
-
-__device__ __forceinline__ uint32_t win_pack_bf16(float lo, float hi) {
-    uint32_t r;
-    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-    return r;
-}
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_c, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_c), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
-}
-
 enum { WIN_FWD1 = 0, WIN_FWD2 = 1, WIN_DGRAD = 2 };
 
 template <int KIND, int CIN, int COUT>
@@ -131,8 +108,8 @@ __device__ __forceinline__ void win_stage_fwd2(const WinArgs& a, int img, float*
         float v[8];
 #pragma unroll
         for (int q = 0; q < 8; ++q) v[q] = (p < 196 && cg * 8 + q < CIN) ? __ldg(src + (cg * 8 + q) * 196 + p) : 0.f;
-        reinterpret_cast<uint4*>(sImg)[i] = make_uint4(win_pack_bf16(v[0], v[1]), win_pack_bf16(v[2], v[3]),
-                                                       win_pack_bf16(v[4], v[5]), win_pack_bf16(v[6], v[7]));
+        reinterpret_cast<uint4*>(sImg)[i] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                       pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
     }
 }
 
@@ -167,7 +144,7 @@ __device__ __forceinline__ void win_stage_fwd1(const WinArgs& a, int img, float*
         float v[8];
 #pragma unroll
         for (int q = 0; q < 8; ++q) v[q] = (p < 1024 && off[q] >= 0) ? sUp[off[q] + p] : 0.f;
-        dst[p] = make_uint4(win_pack_bf16(v[0], v[1]), win_pack_bf16(v[2], v[3]), win_pack_bf16(v[4], v[5]), win_pack_bf16(v[6], v[7]));
+        dst[p] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
     }
     asm volatile("bar.sync 1, %0;" ::"n"(WIN_STAGERS) : "memory");     // sRaw / sUp are reused by the next image
 }
@@ -188,16 +165,10 @@ __device__ __forceinline__ void win_stage_dgrad(const WinArgs& a, int img, float
 }
 
 // ---------------------------------------------------------------------------------------------------
-__device__ __forceinline__ bool elect_one() {
-    uint32_t p;
-    asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(p));
-    return p != 0;
-}
-
 template <class C, int M>
 __device__ __forceinline__ void win_issue(uint32_t tmem, uint32_t s_img, uint32_t s_w, uint32_t bars, int nimg) {
     const bool leader = elect_one();
-    const uint32_t idesc = idesc_bf16(C::NP, 0, 0);
+    const uint32_t idesc = idesc_bf16_m128(C::NP, 0, 0);
     const uint64_t adesc0 = nosw_desc(s_img, C::NPIX * 16u, C::PITCH * 16u);
     const uint64_t bdesc0 = nosw_desc(s_w, C::NP * 16u, 128u);
     const uint32_t acc_bar = bars + 8u * (2 * C::RING);
