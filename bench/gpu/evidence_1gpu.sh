@@ -22,3 +22,4 @@ timeout 600 ncu --set full --clock-control none --import-source on -k "$KF" --la
 timeout 600 ncu --set full --clock-control none --import-source on -k "$KF" --launch-skip 42 -c 14 -f -o gpurun_out/wide_full \
     python bench.py --steps 3 --warmup 3 --no-graph --config wide_cifar > gpurun_out/ncu_full_wide.log 2>&1
 tail -n 2 gpurun_out/ncu_full_lenet.log gpurun_out/ncu_full_wide.log | cut -c1-200
+timeout 120 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; tail -n 1 gpurun_out/smoke.log | cut -c1-200
