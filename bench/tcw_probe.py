@@ -55,7 +55,7 @@ def timed(fn, n=20):
 
 
 ONLY = os.environ.get("TCW_ONLY")            # "wide" / "lenet": one configuration, batch 256, no timing loops (for ncu)
-for swap in (0,):
+for _once in (0,):
     for name, cfg in (("lenet", MNIST_LENET), ("wide", CIFAR_WIDE_LENET)):
         if ONLY and name != ONLY:
             continue
@@ -100,7 +100,7 @@ for swap in (0,):
                 out["pack"] = (0.0, 0.0, tp, "")
             except Exception as e:  # noqa: BLE001
                 out["error"] = repr(e)[:300]
-            print(f"swap={swap} {name} b={b}: " + "  ".join(
+            print(f"{name} b={b}: " + "  ".join(
                 f"{k}: rel={v[0]:.2e} idxdiff={v[1]:.3f} us={v[2]:.1f} cyc={v[3]}" if isinstance(v, tuple) else f"{k}: {v}"
                 for k, v in out.items()), flush=True)
             if "error" in out:
