@@ -95,8 +95,20 @@ class Trainer:
         self.log_interval, self.dry_run, self.global_eval = log_interval, dry_run, global_eval
         self.global_step = 0
         self.no_pump = no_pump
+        self._t_log = None
+        self._steps_at_log = 0
         self._pumps = {}
         self._loss_ring = None
+
+    def _rate(self, n_steps: int, batch: int):
+        """images/s of this rank since the previous log point (host wall clock; the log points are the only host
+        syncs of the loop, so the interval covers exactly the steps between them)."""
+        import time
+        now = time.perf_counter()
+        prev, self._t_log = self._t_log, now
+        if prev is None or n_steps <= 0 or now <= prev:
+            return None
+        return n_steps * batch * self.ctx.world_size / (now - prev)
 
     def _pump_for(self, loader):
         """The native step pump for (stepper, loader), when the combination supports it: native stepper with
@@ -134,7 +146,10 @@ class Trainer:
                 pump.wait_first()
                 last = float(self._loss_ring[c0])
                 self.log.print(train_line(epoch, c0, B, len(loader.dataset), n_batches, last))
-                self.log.event(kind="train", epoch=epoch, step=self.global_step - n + 1, batch_idx=c0, loss=last)
+                first = self.global_step - n + 1
+                self.log.event(kind="train", epoch=epoch, step=first, batch_idx=c0, loss=last,
+                               images_per_s=self._rate(first - self._steps_at_log, B))
+                self._steps_at_log = first
         if run_ragged:                                        # ragged last batch: Python path
             idx = order[n_full * B:]
             x = loader.images.index_select(0, idx).to(self.ctx.device)
@@ -159,7 +174,9 @@ class Trainer:
             if batch_idx % self.log_interval == 0 and self.ctx.is_main:
                 last = float(loss.item())  # the only host sync on the step path (train.py:55)
                 self.log.print(train_line(epoch, batch_idx, len(data), len(loader.dataset), n_batches, last))
-                self.log.event(kind="train", epoch=epoch, step=self.global_step, batch_idx=batch_idx, loss=last)
+                self.log.event(kind="train", epoch=epoch, step=self.global_step, batch_idx=batch_idx, loss=last,
+                               images_per_s=self._rate(self.global_step - self._steps_at_log, len(data)))
+                self._steps_at_log = self.global_step
             if self.dry_run:
                 break
         return last
