@@ -137,3 +137,37 @@ def test_pinned_ring_loader_cpu_semantics():
         orders.append(seen)
     want = sorted((int(base.targets[i]), int(base.images[i].sum())) for i in range(lo, hi))
     assert sorted(orders[0]) == want and sorted(orders[1]) == want and orders[0] != orders[1]
+
+
+def test_bench_contract_without_gpu():
+    """bench.py on a box without CUDA: both arms print one JSON line saying so and exit 0 (the driver's contract)."""
+    import json
+    import subprocess
+    if torch.cuda.is_available():
+        pytest.skip("only meaningful without a GPU")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for impl in ("b200dp", "reference"):
+        r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", impl, "--steps", "2", "--warmup", "1"],
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-500:]
+        line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1]
+        d = json.loads(line)
+        assert d["impl"] == impl and "unavailable" in d
+
+
+def test_native_library_builds_for_sm100a():
+    """The in-tree CUDA library cross-compiles (nvcc, sm_100a) and exports the C ABI of include/b200dp.h."""
+    import ctypes
+    import shutil
+    if shutil.which("nvcc") is None and not os.path.exists("/usr/local/cuda/bin/nvcc"):
+        pytest.skip("no nvcc on this box")
+    from b200dp import build as b
+    lib = b.build()
+    assert os.path.exists(lib) and not b.needs_build()
+    h = ctypes.CDLL(lib)
+    header = open(os.path.join(os.path.dirname(os.path.dirname(lib)), "..", "include", "b200dp.h")).read()
+    import re
+    names = set(re.findall(r"\b(b200dp_[a-z0-9_]+)\s*\(", header))
+    assert len(names) > 30
+    missing = [n for n in sorted(names) if not hasattr(h, n)]
+    assert not missing, missing
