@@ -47,18 +47,27 @@ class NativeLeNet:
 
     def __init__(self, cfg: LeNetConfig, batch: int, device: torch.device, *, loss_mode: str = "ref",
                  spec: ImageSpec = MNIST_SPEC, module: Optional[LeNet] = None, tc: bool = False,
-                 conv_tc: Optional[bool] = None):
+                 conv_tc=None):
         """``tc=True`` routes the five GEMM-shaped layers (conv3, FC.0 and their backward, FC.2's weight
         gradient) through the tcgen05/TMEM/TMA tf32 kernel; ``tc=False`` keeps them in exact fp32 on CUDA cores.
-        ``conv_tc`` does the same for the two 5x5 convolutions (window-tile bf16 tcgen05 kernels).  In tc mode the GEMM operand buffers carry one extra column of ones (the bias
-        gradients fall out of the weight-gradient GEMMs) and are padded to a 16-byte row pitch for TMA."""
+        ``conv_tc`` does the same for the two 5x5 convolutions (window-tile bf16 tcgen05 kernels): ``True`` / ``False``
+        for all of them, or a triple ``(conv1 forward, conv2 forward, convolution backward)`` — the measured-fastest
+        mix for the reference LeNet is ``(False, True, True)`` (profiles/lenet_tc_vs_simt.md).  In tc mode the GEMM
+        operand buffers carry one extra column of ones (the bias gradients fall out of the weight-gradient GEMMs) and
+        are padded to a 16-byte row pitch for TMA."""
         native.load()
         self.cfg, self.B, self.device, self.spec = cfg, int(batch), torch.device(device), spec
         self.tc = bool(tc)
         # convolutions: window-tile tcgen05 kernels (csrc/tc_win.cu, tc_wgrad.cu) or CUDA cores (conv_fwd.cu / conv_bwd.cu).
         # The fused CUDA-core backward only exists for the reference geometry; the wide model needs tc.
-        self.conv_tc = (cfg.width_mult > 1) if conv_tc is None else bool(conv_tc)
-        if cfg.width_mult > 1 and not self.conv_tc:
+        if conv_tc is None:
+            conv_tc = cfg.width_mult > 1
+        if isinstance(conv_tc, (tuple, list)):
+            self.conv1_tc, self.conv2_tc, self.convbwd_tc = (bool(v) for v in conv_tc)
+        else:
+            self.conv1_tc = self.conv2_tc = self.convbwd_tc = bool(conv_tc)
+        self.conv_tc = self.conv1_tc or self.conv2_tc or self.convbwd_tc      # any window-tile kernel in the step
+        if cfg.width_mult > 1 and not self.convbwd_tc:
             raise ValueError("the wide model's convolution backward runs on the tensor-core kernels only")
         self.loss_mode = _LOSS_MODES[loss_mode]
         self.module = module if module is not None else LeNet(cfg)
@@ -100,8 +109,8 @@ class NativeLeNet:
         self.dp2 = torch.empty(B, c.c2 * 25, **f32)
         self.ticket = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.eval_acc = torch.zeros(2, dtype=torch.float64, device=self.device)
-        self.g1 = torch.empty(B, c.c1, 14, 14, **f32) if self.conv_tc else None
-        self._num_partials = native.tcw_conv_wgrad_num_partials if self.conv_tc else native.conv_bwd_num_partials
+        self.g1 = torch.empty(B, c.c1, 14, 14, **f32) if self.convbwd_tc else None
+        self._num_partials = native.tcw_conv_wgrad_num_partials if self.convbwd_tc else native.conv_bwd_num_partials
         # per-tap weight panels of the tensor-core convolutions, re-packed at the start of every forward
         self.wpack = torch.empty(native.tcw_pack_floats(self.dims(B)), **f32) if self.conv_tc else None
         self.n_partials = self._num_partials(self.dims(B))   # rows allocated (full batch)
@@ -115,6 +124,7 @@ class NativeLeNet:
                                   ("ConvNet.1.weight", "ConvNet.1.bias", "ConvNet.4.weight", "ConvNet.4.bias"))
         self.launches_per_step = 0
         self.gemm_ws = native.GemmWorkspace(self.device) if self.tc else None
+        self.pack_stream = torch.cuda.Stream(device=self.device) if (self.conv_tc and not self.conv1_tc) else None
 
     def dims(self, b: int) -> native.Dims:
         c = self.cfg
@@ -125,14 +135,28 @@ class NativeLeNet:
         b = x.shape[0]
         assert b <= self.B and x.is_contiguous() and y.dtype == torch.int64
         d, w = self.dims(b), self.w
-        if self.conv_tc:
+        need_pack = self.conv1_tc or self.conv2_tc or (self.convbwd_tc and train)
+        fork = None
+        if need_pack and not self.conv1_tc and self.pack_stream is not None:
+            # the first layer runs on CUDA cores and needs no packed panels: pack beside it
+            main = torch.cuda.current_stream(self.device)
+            self.pack_stream.wait_stream(main)
+            with torch.cuda.stream(self.pack_stream):
+                native.tcw_pack_weights(w["ConvNet.1.weight"], w["ConvNet.4.weight"], self.wpack, d)
+            fork = main
+        elif need_pack:
             native.tcw_pack_weights(w["ConvNet.1.weight"], w["ConvNet.4.weight"], self.wpack, d)
+        if self.conv1_tc:
             native.tcw_conv1_fwd(x, self.wpack, w["ConvNet.1.bias"], self.p1, self.idx1 if train else None,
                                  d, self.spec.mean, self.spec.std)
-            native.tcw_conv2_fwd(self.p1, self.wpack, w["ConvNet.4.bias"], self.p2, self.idx2 if train else None, d)
         else:
             native.conv1_fwd(x, w["ConvNet.1.weight"], w["ConvNet.1.bias"], self.p1, self.idx1 if train else None,
                              d, self.spec.mean, self.spec.std)
+        if fork is not None:
+            fork.wait_stream(self.pack_stream)
+        if self.conv2_tc:
+            native.tcw_conv2_fwd(self.p1, self.wpack, w["ConvNet.4.bias"], self.p2, self.idx2 if train else None, d)
+        else:
             native.conv2_fwd(self.p1, w["ConvNet.4.weight"], w["ConvNet.4.bias"], self.p2, self.idx2 if train else None, d)
         c = self.cfg
         k3 = c.c2 * 25
@@ -196,7 +220,7 @@ class NativeLeNet:
                 on_bucket(1)
         ow1, ob1, ow2, ob2 = self.conv_offsets
         self.cur_partials = self._num_partials(d)
-        if self.conv_tc:
+        if self.convbwd_tc:
             ld_p2 = self.ld_p2 or k3
             native.tcw_conv2_dgrad(self.dp2, self.p2, self.idx2, self.wpack, self.p1, self.g1, d)
             native.tcw_conv_wgrad(2, self.p1, 0.0, 1.0, self.dp2, self.p2, ld_p2, self.idx2, self.partials,
@@ -219,25 +243,47 @@ class NativeStepper:
 
     def __init__(self, ctx, cfg: LeNetConfig, hyper: OptHyper, *, batch: int, loss_mode: str = "ref",
                  spec: ImageSpec = MNIST_SPEC, algo: str = "auto", graph: bool = True, overlap: bool = True,
-                 dtype: str = "auto", module: Optional[LeNet] = None, conv: str = "auto"):
+                 dtype: str = "auto", module: Optional[LeNet] = None, conv: str = "auto", wire: str = "auto",
+                 timeout_ms: int = 0):
+        """``dtype``: ``fp32`` = every layer on the exact fp32 CUDA-core kernels; ``tf32`` = dense layers on the tcgen05
+        tf32 GEMM; ``bf16`` = additionally the bf16 gradient wire format; ``auto`` = the measured-fastest mix for the
+        model (profiles/lenet_tc_vs_simt.md).  ``conv``: ``simt`` / ``tc`` / ``hybrid`` (first layer on CUDA cores,
+        second layer forward and the whole convolution backward on the bf16 window-tile tcgen05 kernels) / ``auto``.
+        ``algo``: see :class:`b200dp.parallel.p2p.P2PComm`.  ``wire``: ``fp32`` / ``bf16`` gradient lines of the push
+        protocol (``auto``: bf16 only with ``dtype="bf16"``).  ``timeout_ms``: bound on every wait for a peer."""
         self.ctx, self.cfg = ctx, cfg
         self.device = ctx.device
         if dtype not in ("auto", "fp32", "tf32", "bf16"):
             raise ValueError(f"unknown dtype {dtype!r}")
-        if dtype == "auto":
-            # measured on B200 (profiles/): at the reference model's size (GEMMs of <= 25 MFLOP) the CUDA-core
-            # kernels finish sooner than one tcgen05 pipeline fill; the tensor-core path wins for the wide model
-            dtype = "tf32" if cfg.width_mult > 1 else "fp32"
-        self.dtype = "fp32" if dtype == "fp32" else "tf32"      # "bf16" is accepted as a request for the tensor-core path
-        if conv not in ("auto", "simt", "tc"):
+        if conv not in ("auto", "simt", "tc", "hybrid"):
             raise ValueError(f"unknown conv mode {conv!r}")
+        self.requested_dtype = dtype
+        wide = cfg.width_mult > 1
+        if conv == "auto":
+            # measured on B200 with the current kernels (profiles/lenet_tc_vs_simt.md): the first layer (K = 25) is
+            # faster on CUDA cores, everything from the second layer on is faster on the tensor cores
+            conv = "tc" if wide else ("simt" if dtype == "fp32" else "hybrid")
+        if dtype == "auto":
+            dtype = "tf32" if wide else "fp32"      # dense layers: tcgen05 wins from the wide model's sizes on
+        self.dtype = "fp32" if dtype == "fp32" else "tf32"       # GEMM operand type
+        self.conv_mode = conv
+        conv_tc = {"simt": False, "tc": True, "hybrid": (False, True, True)}[conv]
+        if wire == "auto":
+            wire = "bf16" if self.requested_dtype == "bf16" else "fp32"
+        self.wire = wire
         self.net = NativeLeNet(cfg, batch, self.device, loss_mode=loss_mode, spec=spec, module=module,
-                               tc=self.dtype != "fp32", conv_tc=None if conv == "auto" else conv == "tc")
+                               tc=self.dtype != "fp32", conv_tc=conv_tc)
         self.model = self.net.module
         self.arena = self.net.arena
         self.optimizer = FlatOptimizer(self.arena.param, self.arena.grad, hyper)
         self.world = ctx.world_size
-        self.comm = P2PComm(self.arena.layout.total, ctx.rank, self.world, algo) if self.world > 1 else None
+        self.comm = (P2PComm(self.arena.layout.total, ctx.rank, self.world, algo, wire=wire, timeout_ms=timeout_ms)
+                     if self.world > 1 else None)
+        # One launch ends the step (wait for the peers' pushed gradients, sum, average, update the whole arena) when the
+        # model is in the latency regime; big arenas keep one handshake launch per bucket (csrc/reduce_update.cu).
+        from ..parallel.p2p import LL_MAX_ARENA_BYTES
+        small = self.arena.layout.total * 4 <= LL_MAX_ARENA_BYTES
+        self.fused_final = (self.comm.push if self.comm is not None else (small and algo in ("auto", "push")))
         self.use_graph, self.overlap = graph, overlap
         self.side = torch.cuda.Stream(device=self.device) if overlap else None
         self.hyper_dev = torch.zeros(8, dtype=torch.float32, device=self.device)
@@ -252,7 +298,9 @@ class NativeStepper:
         self._warm = 0
         self._comm_off = False        # measurement aid: see set_comm_enabled
         self._pumps = []
-        self.launches_per_step = 14 if self.net.conv_tc else 11   # (1 weight pack +) 5 fwd + 3 (5 with tc convs) bwd + 3 reduce/update
+        n = 5 + (1 if self.net.conv_tc else 0) + 2 + (3 if self.net.convbwd_tc else 1)     # forward, GEMM backward, conv backward
+        n += (1 + (2 if self.world > 1 else 0)) if self.fused_final else 3                 # reduce/update (+ pushes)
+        self.launches_per_step = n
 
     # ---- optimizer scalars live on the device so graph replays see scheduler changes ----
     def _sync_hyper(self) -> None:
@@ -268,7 +316,13 @@ class NativeStepper:
             self.hyper_dev.copy_(self.hyper_host, non_blocking=True)
             self._hyper_cache = vec
 
+    def _comm_struct(self, nbytes: int, overlapped: bool):
+        if self.comm is None or self._comm_off:
+            return None
+        return self.comm.struct_for(nbytes, overlapped=overlapped)
+
     def _reduce_update(self, bucket_index: int) -> None:
+        """Handshake protocol: one fused reduce + average + update launch per bucket."""
         net, opt = self.net, self.optimizer
         b = self.arena.layout.buckets[bucket_index]
         is_conv = bucket_index == 2
@@ -276,25 +330,57 @@ class NativeStepper:
                              net.partials if is_conv else None, net.cur_partials if is_conv else 0,
                              net.partial_stride if is_conv else 0, opt.hyper.code(), self.hyper_dev,
                              self.step_counter, bucket_index == 2,
-                             self.comm.struct_for(b.numel * 4, overlapped=self.overlap and bucket_index != 2)
-                             if (self.comm and not self._comm_off) else None,
+                             self._comm_struct(b.numel * 4, self.overlap and bucket_index != 2),
                              net.loss, self.loss_sink)
+
+    def _push(self, bucket_index: int) -> None:
+        """Push protocol: send a finished bucket to every peer, wait for nobody."""
+        cs = self._comm_struct(0, False)
+        if cs is not None:
+            b = self.arena.layout.buckets[bucket_index]
+            native.grad_push(self.arena.grad, b.start, b.numel, self.step_counter, cs)
+
+    def _final_update(self, pushed: bool) -> None:
+        """Push protocol: the step's single wait + sum + average + update launch over the whole arena; it sums the
+        convolution backward's partial rows and pushes that bucket itself."""
+        net, opt = self.net, self.optimizer
+        conv = self.arena.layout.buckets[2]
+        native.reduce_update_ll(self.arena.param, self.arena.grad, opt.state0, opt.state1, None, 0,
+                                self.arena.layout.total, net.partials, net.cur_partials, net.partial_stride,
+                                conv.start, conv.numel, not pushed, opt.hyper.code(), self.hyper_dev,
+                                self.step_counter, self._comm_struct(0, False), net.loss, self.loss_sink)
 
     def _step_body(self, x: torch.Tensor, y: torch.Tensor) -> None:
         main = torch.cuda.current_stream(self.device)
         self.net.forward(x, y, train=True)
+        side = self.side
 
         def on_bucket(i: int) -> None:
-            if self.side is None:
+            if self.fused_final:
+                last = i == 2
+                if side is None:                     # no overlap: everything after backward, in one launch
+                    if last:
+                        self._final_update(pushed=False)
+                    return
+                if not last and (self.comm is None or self._comm_off):
+                    return                           # nothing to send at world size 1
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    if last:
+                        self._final_update(pushed=True)
+                    else:
+                        self._push(i)
+                return
+            if side is None:
                 self._reduce_update(i)
                 return
-            self.side.wait_stream(main)
-            with torch.cuda.stream(self.side):
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
                 self._reduce_update(i)
 
         self.net.backward(x, on_bucket)
-        if self.side is not None:
-            main.wait_stream(self.side)
+        if side is not None:
+            main.wait_stream(side)
 
     def train_step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         self._sync_hyper()
@@ -364,13 +450,21 @@ class NativeStepper:
 
     # ---- bookkeeping -----------------------------------------------------------------
     def params_changed(self) -> None:
-        """Call after loading a checkpoint: re-seed the device generation counter."""
+        """Call after loading a checkpoint (collective at world > 1): re-seed the device generation counter and
+        forget the generation numbers the peers have seen."""
         self.step_counter[0] = self.optimizer.step_count
         self._hyper_cache = None
+        if self.comm is not None:
+            self.comm.reset()
+
+    def error_flag(self) -> int:
+        """The device's sticky error word (one D2H read; call at points that synchronise anyway)."""
+        return int(self.step_counter[2].item())
 
     def check_error(self) -> None:
-        if int(self.step_counter[2].item()) != 0:
-            raise RuntimeError("a peer rank did not publish its gradients within the spin bound (dead rank?)")
+        if self.error_flag() != 0:
+            raise RuntimeError("a peer rank did not deliver its gradients within the time bound (dead or stalled "
+                               "rank?); this rank stopped updating its parameters at that step")
 
     @torch.no_grad()
     def replica_divergence(self) -> float:

@@ -41,7 +41,8 @@ class TcProblem(C.Structure):
 class Comm(C.Structure):
     _fields_ = [("world", C.c_int), ("rank", C.c_int), ("algo", C.c_int),
                 ("stage", C.c_void_p * 8), ("flags", C.c_void_p * 8), ("mc_stage", C.c_void_p),
-                ("arena_len", C.c_int), ("max_slices", C.c_int), ("max_ctas", C.c_int)]
+                ("arena_len", C.c_int), ("max_slices", C.c_int), ("max_ctas", C.c_int),
+                ("ll", C.c_void_p * 8), ("wire", C.c_int), ("timeout_ms", C.c_uint32)]
 
 
 class PumpDesc(C.Structure):
@@ -94,8 +95,11 @@ def load(build_if_missing: bool = True):
     lib.b200dp_tcw_set_debug.restype = None
     lib.b200dp_conv_bwd.argtypes = [vp, i, f, f, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, Dims, vp]
     lib.b200dp_reduce_update.argtypes = [vp, vp, vp, vp, vp, i, i, vp, i, i, i, vp, vp, i, C.POINTER(Comm), vp, vp, vp]
+    lib.b200dp_grad_push.argtypes = [vp, i, i, vp, C.POINTER(Comm), vp]
+    lib.b200dp_reduce_update_ll.argtypes = [vp, vp, vp, vp, vp, i, i, vp, i, i, i, i, i, i, vp, vp, C.POINTER(Comm), vp, vp, vp]
     lib.b200dp_symm_alloc.argtypes = [C.POINTER(vp), C.c_uint64]
     lib.b200dp_symm_free.argtypes = [vp]
+    lib.b200dp_symm_zero.argtypes = [vp, C.c_uint64]
     lib.b200dp_symm_export.argtypes = [vp, C.c_char_p]
     lib.b200dp_symm_import.argtypes = [C.c_char_p, C.POINTER(vp)]
     lib.b200dp_symm_close.argtypes = [vp]
@@ -273,11 +277,31 @@ def reduce_update(param, grad, state0, state1, shadow, start: int, count: int, p
                                       _stream()), "reduce_update")
 
 
+def grad_push(grad, start: int, count: int, step_counter, comm: Comm) -> None:
+    """Fire-and-forget: write grad[start, start+count) into every peer's receive area (csrc/ll_reduce.cu)."""
+    check(load().b200dp_grad_push(_p(grad), start, count, _p(step_counter), C.byref(comm), _stream()), "grad_push")
+
+
+def reduce_update_ll(param, grad, state0, state1, shadow, start: int, count: int, partials, n_partials: int,
+                     partial_stride: int, p_start: int, p_count: int, push_rest: bool, opt_kind: int, hyper,
+                     step_counter, comm: Optional[Comm], loss_src=None, loss_sink=None) -> None:
+    """The step's single wait + rank-order sum + average + optimizer launch of the push protocol."""
+    check(load().b200dp_reduce_update_ll(_p(param), _p(grad), _p(state0), _p(state1), _p(shadow), start, count,
+                                         _p(partials), n_partials, partial_stride, p_start, p_count, int(push_rest),
+                                         opt_kind, _p(hyper), _p(step_counter),
+                                         C.byref(comm) if comm is not None else None, _p(loss_src), _p(loss_sink),
+                                         _stream()), "reduce_update_ll")
+
+
 # ---- symmetric memory ------------------------------------------------------------
 def symm_alloc(nbytes: int) -> int:
     ptr = C.c_void_p()
     check(load().b200dp_symm_alloc(C.byref(ptr), nbytes), "symm_alloc")
     return ptr.value
+
+
+def symm_zero(ptr: int, nbytes: int) -> None:
+    check(load().b200dp_symm_zero(ptr, nbytes), "symm_zero")
 
 
 def symm_free(ptr: int) -> None:

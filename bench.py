@@ -52,11 +52,16 @@ def _parse():
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--no-overlap", action="store_true")
     p.add_argument("--no-pump", action="store_true", help="e2e: drive every step from Python")
-    p.add_argument("--conv", choices=["auto", "simt", "tc"], default="auto",
-                   help="convolution kernels: CUDA-core fp32 or window-tile tcgen05 (auto: by model size)")
+    p.add_argument("--conv", choices=["auto", "simt", "tc", "hybrid"], default="auto",
+                   help="convolution kernels: CUDA-core fp32, window-tile tcgen05 (bf16 operands), or hybrid = first layer "
+                        "on CUDA cores + everything after it on tcgen05 (auto: measured-fastest for the model)")
+    p.add_argument("--algo", choices=["auto", "push", "oneshot", "twoshot", "nvls"], default="auto",
+                   help="gradient all-reduce protocol (auto: push for whole-model gradients up to 1 MB)")
+    p.add_argument("--wire", choices=["auto", "fp32", "bf16"], default="auto", help="gradient wire format of the push protocol")
     p.add_argument("--input", choices=["u8", "f32"], default="u8", help="host->device input format (e2e)")
-    p.add_argument("--dtype", choices=["auto", "fp32", "tf32"], default="auto",
-                   help="tf32 = tcgen05 tensor-core GEMMs on fp32 tensors; fp32 = exact CUDA-core kernels")
+    p.add_argument("--dtype", choices=["auto", "fp32", "tf32", "bf16"], default="auto",
+                   help="fp32 = exact CUDA-core kernels everywhere; tf32 = tcgen05 GEMMs on fp32 tensors; bf16 = bf16 "
+                        "tcgen05 convolutions + bf16 gradient wire; auto = measured-fastest mix")
     return p.parse_args()
 
 
@@ -99,6 +104,22 @@ def _model_cfg(name):
     return MNIST_LENET, MNIST_SPEC
 
 
+def _dtype_label(stepper):
+    """What actually computes: bf16 wherever a tcgen05 convolution runs, tf32 for tcgen05 GEMMs, fp32 elsewhere."""
+    net = stepper.net
+    parts = []
+    if net.conv_tc:
+        which = [n for n, on in (("conv1 fprop", net.conv1_tc), ("conv2 fprop", net.conv2_tc),
+                                 ("conv dgrad+wgrad", net.convbwd_tc)) if on]
+        parts.append("bf16 tcgen05 (" + ", ".join(which) + ")")
+    if stepper.dtype != "fp32":
+        parts.append("tf32 tcgen05 GEMMs")
+    if not parts:
+        return "fp32"
+    rest = "fp32 CUDA cores elsewhere" if not (net.conv1_tc and stepper.dtype != "fp32") else "fp32 head"
+    return "bf16: " + " + ".join(parts) + "; " + rest + "; fp32 accumulation, storage and master weights"
+
+
 def run_own(args):
     from b200dp.data.synthetic import PinnedRingLoader
     from b200dp.models.fused import NativeStepper
@@ -114,7 +135,8 @@ def run_own(args):
     torch.manual_seed(5)
     stepper = NativeStepper(ctx, cfg, OptHyper(args.optimizer, lr=0.1 if args.optimizer == "adadelta" else 0.01),
                             batch=batch, loss_mode="ref", spec=spec, graph=not args.no_graph,
-                            overlap=not args.no_overlap, dtype=args.dtype, conv=args.conv)
+                            overlap=not args.no_overlap, dtype=args.dtype, conv=args.conv, algo=args.algo,
+                            wire=args.wire)
     K, W = args.steps, args.warmup
 
     # ---- device-resident input pool larger than L2, cycled (timing rule) ----
@@ -200,9 +222,7 @@ def run_own(args):
             "ms_per_step": ms / K, "higher_is_better": True,
             "scaling": "strong" if args.config == "strong4096" else "weak",
             "vs_baseline": None,
-            "dtype": ("fp32" if stepper.dtype == "fp32" else
-                      "tf32 tcgen05 GEMMs" + (" + bf16 tcgen05 convolutions (fprop, dgrad, wgrad)" if stepper.net.conv_tc
-                                              else " + fp32 CUDA-core convs") + " (fp32 storage, accumulation and master weights)"),
+            "dtype": _dtype_label(stepper),
             "data": "synthetic", "impl": "b200dp",
             "config": {"model": "cnn.py LeNet" if args.config != "wide_cifar" else "cnn.py LeNet 4x wide, CIFAR-shaped",
                        "global_batch": batch * world, "per_gpu_batch": batch, "seq_len": None,
@@ -210,7 +230,9 @@ def run_own(args):
                        "parallelism": f"dp{world}", "optimizer": args.optimizer, "loss": "ref (nll on softmax probs)",
                        "l2": f"inputs cycle through a {n_pool * batch * img_bytes >> 20} MiB device pool (> 126 MiB L2)",
                        "cuda_graph": not args.no_graph, "overlap": not args.no_overlap,
-                       "allreduce": "fused one-shot P2P reduce+average+update kernel" if world > 1 else "n/a (1 GPU)"},
+                       "allreduce": (("push protocol: per-bucket P2P pushes + one fused wait/sum/average/update kernel, "
+                                      + stepper.wire + " wire") if stepper.fused_final else
+                                     "fused per-bucket P2P reduce+average+update kernel") if world > 1 else "n/a (1 GPU)"},
             "clocks": clocks,
             "e2e": {"value": imgs / (e2e_ms / 1e3), "unit": "images/s", "ms_per_step": e2e_ms / K,
                     "h2d_bytes_per_step": loader.h2d_bytes_per_batch, "d2h_bytes_per_step": 4,

@@ -20,7 +20,7 @@
 //      optional bf16 shadow copy for the tensor-core kernels; averaged gradient written back.
 // The generation counter lives on the device and is advanced by the last CTA of the step's last
 // bucket, so the same launch sequence can be replayed from a CUDA graph.
-#include "common.cuh"
+#include "opt_math.cuh"
 
 namespace b200dp {
 
@@ -31,7 +31,7 @@ constexpr int RU_MAX_CTAS = 148 * 2;  // = resident CTAs (2 per SM at this regis
 constexpr int RU_UNROLL = 4;          // chunks whose loads are issued together
 constexpr int RU_PSLICE = 128;        // floats per CTA when partial rows are pre-reduced (32 float4 columns x 8 row groups)
 constexpr int RU_FLAG_GRAIN = 32;     // one flag slot per 32 arena floats
-constexpr unsigned RU_SPIN_LIMIT = 1u << 28;
+constexpr unsigned long long RU_DEFAULT_TIMEOUT_NS = 20ull * 1000ull * 1000ull * 1000ull;
 
 struct RUArgs {
     float* param; float* grad; float* state0; float* state1; uint16_t* shadow;
@@ -72,92 +72,16 @@ __device__ __forceinline__ void multimem_st_f4(float* mc, const float4& v) {
     asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
                  ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
-__device__ __forceinline__ uint16_t f32_to_bf16_rn(float f) {
-    uint32_t u = __float_as_uint(f);
-    if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40u);
-    u += 0x7fffu + ((u >> 16) & 1u);
-    return (uint16_t)(u >> 16);
-}
-
-struct OptScalars { float lr, h0, h1, h2, wd, c0, c1; };
-
-// Every operation is an explicit round-to-nearest intrinsic: the compiler may not contract or
-// re-associate, so the two code paths of the two-shot algorithm (owner / non-owner) and every rank
-// produce bit-identical parameters from the same summed gradient.
-__device__ __forceinline__ void opt_apply(int kind, const OptScalars& h, float g, float& p, float& s0, float& s1) {
-    if (h.wd != 0.f) g = __fmaf_rn(h.wd, p, g);
-    if (kind == 0) {            // Adadelta: h0 = rho, h1 = eps
-        const float omr = __fsub_rn(1.f, h.h0);
-        s0 = __fmaf_rn(h.h0, s0, __fmul_rn(omr, __fmul_rn(g, g)));
-        const float stdv = __fsqrt_rn(__fadd_rn(s0, h.h1));
-        const float delta = __fmul_rn(__fdiv_rn(__fsqrt_rn(__fadd_rn(s1, h.h1)), stdv), g);
-        s1 = __fmaf_rn(h.h0, s1, __fmul_rn(omr, __fmul_rn(delta, delta)));
-        p = __fsub_rn(p, __fmul_rn(h.lr, delta));
-    } else if (kind == 1) {     // SGD: h0 = momentum, h1 = nesterov flag
-        float d = g;
-        if (h.h0 != 0.f) {
-            s0 = __fmaf_rn(h.h0, s0, g);
-            d = (h.h1 != 0.f) ? __fmaf_rn(h.h0, s0, g) : s0;
-        }
-        p = __fsub_rn(p, __fmul_rn(h.lr, d));
-    } else {                    // Adam: h0 = beta1, h1 = beta2, h2 = eps; c0 = 1/bc1, c1 = 1/sqrt(bc2)
-        s0 = __fmaf_rn(h.h0, s0, __fmul_rn(__fsub_rn(1.f, h.h0), g));
-        s1 = __fmaf_rn(h.h1, s1, __fmul_rn(__fsub_rn(1.f, h.h1), __fmul_rn(g, g)));
-        const float denom = __fmaf_rn(__fsqrt_rn(s1), h.c1, h.h2);
-        p = __fsub_rn(p, __fmul_rn(__fmul_rn(h.lr, h.c0), __fdiv_rn(s0, denom)));
-    }
-}
-
-__device__ __forceinline__ float4 scale4(const float4& v, float k) {
-    return make_float4(__fmul_rn(v.x, k), __fmul_rn(v.y, k), __fmul_rn(v.z, k), __fmul_rn(v.w, k));
-}
-__device__ __forceinline__ float4 add4(const float4& a, const float4& b) {
-    return make_float4(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z), __fadd_rn(a.w, b.w));
-}
-
-struct RUCtx {
-    OptScalars h;
-    int kind;
-    float* param; float* grad; float* state0; float* state1; uint16_t* shadow;
-};
-
-// The update of one float4 is split into its loads and its math+stores so that a loop can put the loads of
-// several chunks in flight before the first dependent instruction (one chunk at a time is latency-bound:
-// 16 bytes per thread per memory round trip).
-struct RULoaded { float4 p, s0, s1; };
-__device__ __forceinline__ RULoaded ru_load(const RUCtx& c, int idx) {
-    RULoaded L;
-    L.p = *reinterpret_cast<const float4*>(c.param + idx);
-    L.s0 = *reinterpret_cast<const float4*>(c.state0 + idx);
-    L.s1 = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (c.kind != 1) L.s1 = *reinterpret_cast<const float4*>(c.state1 + idx);
-    return L;
-}
-__device__ __forceinline__ void ru_apply(const RUCtx& c, int idx, float4 g, RULoaded L) {
-    float4 p = L.p, s0 = L.s0, s1 = L.s1;
-    const bool two = (c.kind != 1);
-    opt_apply(c.kind, c.h, g.x, p.x, s0.x, s1.x);
-    opt_apply(c.kind, c.h, g.y, p.y, s0.y, s1.y);
-    opt_apply(c.kind, c.h, g.z, p.z, s0.z, s1.z);
-    opt_apply(c.kind, c.h, g.w, p.w, s0.w, s1.w);
-    *reinterpret_cast<float4*>(c.param + idx) = p;
-    *reinterpret_cast<float4*>(c.state0 + idx) = s0;
-    if (two) *reinterpret_cast<float4*>(c.state1 + idx) = s1;
-    *reinterpret_cast<float4*>(c.grad + idx) = g;     // param.grad == mean over ranks, like train.py:39
-    if (c.shadow) {
-        uint2 packed;
-        packed.x = (uint32_t)f32_to_bf16_rn(p.x) | ((uint32_t)f32_to_bf16_rn(p.y) << 16);
-        packed.y = (uint32_t)f32_to_bf16_rn(p.z) | ((uint32_t)f32_to_bf16_rn(p.w) << 16);
-        *reinterpret_cast<uint2*>(c.shadow + idx) = packed;
-    }
-}
-__device__ __forceinline__ void ru_update(const RUCtx& c, int idx, float4 g) { ru_apply(c, idx, g, ru_load(c, idx)); }
-
 // spin until *flag >= gen (generation numbers only grow); bounded so a dead peer is an error, not a hang
-__device__ __forceinline__ bool ru_wait(const uint32_t* flag, uint32_t gen) {
+__device__ __forceinline__ bool ru_wait(const uint32_t* flag, uint32_t gen, unsigned long long timeout_ns) {
     unsigned spins = 0;
+    unsigned long long t0 = 0;
     while ((int)(ld_acquire_sys(flag) - gen) < 0) {
-        if (++spins > RU_SPIN_LIMIT) return false;
+        if ((++spins & 255u) == 0u) {
+            const unsigned long long now = globaltimer_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > timeout_ns) return false;
+        }
         __nanosleep(20);
     }
     return true;
@@ -179,40 +103,14 @@ __global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
     RUCtx cx;
     cx.kind = a.opt_kind; cx.param = a.param; cx.grad = a.grad; cx.state0 = a.state0; cx.state1 = a.state1;
     cx.shadow = a.shadow;
-    cx.h.lr = a.hyper[0]; cx.h.h0 = a.hyper[1]; cx.h.h1 = a.hyper[2]; cx.h.h2 = a.hyper[3]; cx.h.wd = a.hyper[4];
-    cx.h.c0 = cx.h.c1 = 1.f;
-    if (a.opt_kind == 2) {
-        const float t = (float)gen;
-        cx.h.c0 = 1.f / (1.f - powf(cx.h.h0, t));
-        cx.h.c1 = rsqrtf(1.f - powf(cx.h.h1, t));
-    }
+    ru_load_hyper(cx, a.hyper, gen);
+    const unsigned long long timeout_ns =
+        a.comm.timeout_ms ? (unsigned long long)a.comm.timeout_ms * 1000000ull : RU_DEFAULT_TIMEOUT_NS;
 
     // ---- A: (optional) sum the partial-gradient rows of this 32-float slice, fixed order ----
     const bool from_rows = a.partials != nullptr;
     if (from_rows) {
-        const int o = tid & 31, pg = tid >> 5;            // thread (o, pg) sums float4 column o of rows pg, pg+8, ...; then 8 -> 1
-        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (o * 4 < n_here) {
-            const float* src = a.partials + off + o * 4;  // off and partial_stride are multiples of 4: 16-byte aligned
-            int r = pg;
-            for (; r + 56 < a.n_partials; r += 64) {      // 8 independent loads in flight, added in row order
-                float4 t[8];
-#pragma unroll
-                for (int u = 0; u < 8; ++u) t[u] = __ldcg(reinterpret_cast<const float4*>(src + (long)(r + 8 * u) * a.partial_stride));
-#pragma unroll
-                for (int u = 0; u < 8; ++u) s = add4(s, t[u]);
-            }
-            for (; r < a.n_partials; r += 8) s = add4(s, __ldcg(reinterpret_cast<const float4*>(src + (long)r * a.partial_stride)));
-        }
-        *reinterpret_cast<float4*>(&sRed[pg][o * 4]) = s;
-        __syncthreads();
-        if (tid < 32) {
-            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-            for (int q = 0; q < 8; ++q) t = add4(t, *reinterpret_cast<const float4*>(&sRed[q][tid * 4]));
-            *reinterpret_cast<float4*>(sSlice + tid * 4) = t;
-        }
-        __syncthreads();
+        ru_sum_partial_rows(a.partials, a.n_partials, a.partial_stride, off, n_here, sRed, sSlice, tid);
     }
     auto active = [&](int c) { return c * RU_CHUNK + tid * 4 < n_here; };
     auto local_g = [&](int c) -> float4 {
@@ -220,6 +118,10 @@ __global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
                          : *reinterpret_cast<const float4*>(a.grad + base_idx + c * RU_CHUNK);
     };
 
+    // A time-out (here or in an earlier step: the error word is sticky) skips the exchange and the update but not the
+    // bookkeeping below, so the generation keeps advancing and the loss-ring indices stay defined.
+    do {
+    if (a.step_counter[2] != 0u) break;
     if (world == 1) {
         for (int c0 = 0; c0 < chunks; c0 += RU_UNROLL) {
             float4 g[RU_UNROLL];
@@ -272,12 +174,12 @@ __global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
                 for (int r = 0; r < 8; ++r)
                     if (r == tid) peer_flags = a.comm.flags[r];
                 st_release_sys(peer_flags + (long)rank * a.comm.max_slices + slot, gen);
-                if (!ru_wait(my_flags + (long)tid * a.comm.max_slices + slot, gen)) sTimeout = 1;
+                if (!ru_wait(my_flags + (long)tid * a.comm.max_slices + slot, gen, timeout_ns)) sTimeout = 1;
             }
             __syncthreads();
             if (sTimeout) {
                 if (tid == 0) atomicExch(a.step_counter + 2, 1u);
-                return;   // leave parameters untouched; the host sees the error flag
+                break;    // parameters stay untouched; the host sees the error flag; the ticket below is still taken
             }
             for (int c = 0; c < chunks; ++c) {
                 if (active(c)) {
@@ -300,12 +202,12 @@ __global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
                     for (int r = 0; r < 8; ++r)
                         if (r == owner) owner_flags = a.comm.flags[r];
                     st_release_sys(owner_flags + (long)rank * a.comm.max_slices + slot, gen);   // "my slice is up"
-                    if (!ru_wait(flags2_mine + slot, gen)) sTimeout = 1;                          // "the sum is here"
+                    if (!ru_wait(flags2_mine + slot, gen, timeout_ns)) sTimeout = 1;                          // "the sum is here"
                 }
                 __syncthreads();
                 if (sTimeout) {
                     if (tid == 0) atomicExch(a.step_counter + 2, 1u);
-                    return;
+                    break;
                 }
                 for (int c0 = 0; c0 < chunks; c0 += RU_UNROLL) {
                     float4 t[RU_UNROLL];
@@ -322,11 +224,11 @@ __global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
                 }
             } else {
                 if (tid < world && tid != rank)
-                    if (!ru_wait(my_flags + (long)tid * a.comm.max_slices + slot, gen)) sTimeout = 1;
+                    if (!ru_wait(my_flags + (long)tid * a.comm.max_slices + slot, gen, timeout_ns)) sTimeout = 1;
                 __syncthreads();
                 if (sTimeout) {
                     if (tid == 0) atomicExch(a.step_counter + 2, 1u);
-                    return;
+                    break;
                 }
                 if (a.comm.algo == 2) {
                     // NVLS: the in-switch reductions of several chunks are in flight together
@@ -375,27 +277,10 @@ __global__ void __launch_bounds__(RU_NT, 2) reduce_update_kernel(RUArgs a) {
         }
     }
 
+    } while (false);
+
     // ---- generation counter: advanced once per step by the last CTA of the last bucket ----
-    if (a.last_bucket) {
-        __syncthreads();
-        if (tid == 0) {
-            __threadfence();
-            if (atomicAdd(a.step_counter + 1, 1u) == gridDim.x - 1) {
-                if (a.loss_sink != nullptr) {
-                    // deliver the step's loss to the host: a 4-byte store into a mapped pinned array
-                    // (no copy command, nothing for the next step to wait on)
-                    const unsigned long long ring = a.loss_sink[0], idx = (unsigned long long)gen - a.loss_sink[1];
-                    if (ring != 0ull && idx < a.loss_sink[2]) {
-                        reinterpret_cast<volatile float*>(ring)[idx] = __ldcg(a.loss_src);
-                        __threadfence_system();
-                    }
-                }
-                a.step_counter[1] = 0u;
-                __threadfence();
-                a.step_counter[0] = gen;
-            }
-        }
-    }
+    if (a.last_bucket) ru_finish_step(a.step_counter, gen, gridDim.x, a.loss_src, a.loss_sink, tid);
 }
 
 }  // namespace b200dp

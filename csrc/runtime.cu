@@ -32,6 +32,12 @@ extern "C" int b200dp_symm_alloc(void** ptr, uint64_t bytes) {
     B200DP_CHECK(cudaDeviceSynchronize());
     return 0;
 }
+extern "C" int b200dp_symm_zero(void* ptr, uint64_t bytes) {
+    B200DP_REQUIRE(ptr != nullptr && bytes > 0, "bad arguments");
+    B200DP_CHECK(cudaMemset(ptr, 0, bytes));
+    B200DP_CHECK(cudaDeviceSynchronize());
+    return 0;
+}
 extern "C" int b200dp_symm_free(void* ptr) {
     B200DP_CHECK(cudaFree(ptr));
     return 0;

@@ -204,7 +204,8 @@ int b200dp_conv_bwd_noalloc(const void* x, int in_is_u8, float mean, float std, 
  * device from the generation number).  Read on the device so a captured CUDA graph sees
  * scheduler changes.
  * step_counter (device, uint32[4], zero-initialised): [0] generation (= optimizer steps done),
- * [1] ticket, [2] error flag (1 = a peer did not answer within the spin bound).  The LAST
+ * [1] ticket, [2] error word (1 = a peer did not answer within comm->timeout_ms; sticky: later launches
+ * skip the exchange and the update but keep the bookkeeping going).  The LAST
  * bucket launch of a step (last_bucket != 0) advances the generation.
  * loss_src / loss_sink (both nullable; used by the last bucket launch only): loss_sink is a device
  * uint64[3] = {address of a mapped pinned float array (0 = off), generation stored at index 0,
@@ -228,6 +229,13 @@ typedef struct {
                                  run should use few CTAs (32): CTAs that spin on a slow peer's flags would otherwise hold
                                  the SMs the backward kernels need, and with several chunks in flight per thread a few
                                  CTAs already cover the NVLink latency-bandwidth product */
+    /* ---- push protocol (b200dp_grad_push / b200dp_reduce_update_ll; ignored by b200dp_reduce_update) ---- */
+    uint32_t* ll[8];          /* every rank's receive area (peer-mapped, zero-initialised):
+                                 [2 parities][8 source ranks][arena_len x 2 words] of flagged 8-byte lines */
+    int wire;                 /* gradient wire format of the push protocol: 0 = fp32 lines {float, gen},
+                                 1 = bf16 lines {2 x bf16, gen} (half the NVLink bytes; fp32 accumulation) */
+    uint32_t timeout_ms;      /* bound on every wait for a peer (0 = 20 s): a peer that does not deliver raises
+                                 step_counter[2] instead of hanging the GPU (both protocols) */
 } b200dp_comm;
 
 int b200dp_reduce_update(float* param, float* grad, float* state0, float* state1, uint16_t* shadow_bf16,
@@ -236,10 +244,35 @@ int b200dp_reduce_update(float* param, float* grad, float* state0, float* state1
                          const b200dp_comm* comm, const float* loss_src, const uint64_t* loss_sink,
                          b200dp_stream_t s);
 
+/* Push form of the same product kernel, for whole-model gradients in the latency regime (<= ~1 MB; the reference
+ * LeNet is 247 KB).  Replaces train.py:34-39 + train.py:51 like b200dp_reduce_update, with ONE exposed wait per
+ * step instead of one handshake per bucket:
+ *   b200dp_grad_push         as soon as backward has produced grad[start, start+count), write it into every
+ *                            peer's receive area (comm->ll) as 8-byte lines {payload, generation} over NVLink;
+ *                            returns without waiting for anybody.
+ *   b200dp_reduce_update_ll  ends the step for the arena range [start, start+count): sums the partial rows of the
+ *                            sub-range [p_start, p_start+p_count) (rows' column i == arena element p_start+i;
+ *                            partials NULL / p_count 0: none) and pushes that sub-range itself, pushes the rest
+ *                            too when push_rest != 0 (nobody called b200dp_grad_push this step), then for every
+ *                            element waits for the peers' lines in LOCAL memory, adds in rank order, scales by
+ *                            1/world, applies the optimizer, advances the generation (always the step's last
+ *                            launch) and delivers the loss (loss_src / loss_sink as in b200dp_reduce_update).
+ * comm may be NULL (or world 1): plain local update.  A wait that exceeds comm->timeout_ms raises the sticky
+ * error word step_counter[2]; from then on every launch of either protocol only does its bookkeeping. */
+int b200dp_grad_push(const float* grad, int start, int count, const uint32_t* step_counter,
+                     const b200dp_comm* comm, b200dp_stream_t s);
+int b200dp_reduce_update_ll(float* param, float* grad, float* state0, float* state1, uint16_t* shadow_bf16,
+                            int start, int count, const float* partials, int n_partials, int partial_stride,
+                            int p_start, int p_count, int push_rest, int opt_kind, const float* hyper,
+                            uint32_t* step_counter, const b200dp_comm* comm, const float* loss_src,
+                            const uint64_t* loss_sink, b200dp_stream_t s);
+
 /* ---- symmetric memory plumbing (replaces the NCCL communicator of train.py:26-31) ----
  * Allocation of peer-mappable device memory and exchange via CUDA IPC handles
  * (64 opaque bytes each, shipped between ranks by torch.distributed at start-up). */
 int b200dp_symm_alloc(void** ptr, uint64_t bytes);           /* cudaMalloc + zero */
+int b200dp_symm_zero(void* ptr, uint64_t bytes);             /* cudaMemset + synchronize: forget all generations
+                                                                (callers that move the step counter back; collective) */
 int b200dp_symm_free(void* ptr);
 int b200dp_symm_export(void* ptr, uint8_t handle_out[64]);
 int b200dp_symm_import(const uint8_t handle[64], void** ptr_out);
