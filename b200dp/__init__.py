@@ -12,7 +12,7 @@ Sub-packages
     ops       ctypes bindings to the in-tree CUDA library (csrc/, include/)
     optim     flat fused optimizers (Adadelta / SGD-momentum / Adam) + StepLR
     parallel  process-group bootstrap, symmetric arena, DataParallel wrap
-    utils     timing, logging, clocks sampling
+    utils     logging, clocks sampling
 """
 
 __version__ = "0.1.0"

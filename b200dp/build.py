@@ -19,8 +19,7 @@ OUT_DIR = os.path.join(ROOT, "b200dp", "_native")
 OBJ_DIR = os.path.join(OUT_DIR, "obj")
 LIB = os.path.join(OUT_DIR, "libb200dp.so")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-NVCC_FLAGS = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "--use_fast_math=false",
-              "-Xptxas", "-v", "--expt-relaxed-constexpr"]
+NVCC_FLAGS = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]   # no fast-math: parity tests
 
 
 def _nvcc() -> str:
@@ -49,7 +48,7 @@ def _compile(src: str, log_dir: str) -> str:
                 glob.glob(os.path.join(ROOT, "include", "*.h")))
     if os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(src), hdr_m):
         return obj
-    cmd = [_nvcc(), *ARCH, *[f for f in NVCC_FLAGS if f != "--use_fast_math=false"], "-I", os.path.join(ROOT, "include"),
+    cmd = [_nvcc(), *ARCH, *NVCC_FLAGS, "-I", os.path.join(ROOT, "include"),
            "-c", src, "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     with open(os.path.join(log_dir, os.path.basename(src) + ".log"), "w") as f:

@@ -52,7 +52,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--test-size", type=int, default=10000)
     p.add_argument("--width-mult", type=int, default=1)
     p.add_argument("--bucket-bytes", type=int, default=-1, help="<=0: layer-aligned LeNet buckets")
-    p.add_argument("--allreduce-algo", choices=["auto", "oneshot", "twoshot", "nvls"], default="auto")
+    p.add_argument("--allreduce-algo", choices=["auto", "push", "oneshot", "twoshot", "nvls"], default="auto",
+                   help="push = per-bucket P2P pushes + one wait/sum/update launch per step (whole-model gradients up to "
+                        "1 MB); oneshot/twoshot/nvls = one handshake launch per bucket; auto = by size")
     p.add_argument("--no-overlap", action="store_true", help="reduce after backward, not during it")
     p.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
     p.add_argument("--no-pump", action="store_true",
@@ -87,7 +89,7 @@ def main(argv: Optional[Sequence[str]] = None) -> int:
     if launch.launched_by_torchrun():
         launch.init_from_env(run, args, backend=None if use_cuda else "gloo", use_cuda=use_cuda)
         return 0
-    world = args.world_size or (torch.cuda.device_count() if use_cuda else 2)
+    world = args.world_size or (launch.discover_world_size(args.no_cuda) if use_cuda else 2)
     launch.spawn(run, args, world, backend=None if use_cuda else "gloo", use_cuda=use_cuda,
                  port=args.master_port)
     return 0

@@ -163,3 +163,15 @@ def shard_for_rank(dataset, rank: int, world_size: int, *, compat: bool = False)
     """The train.py:86-93 idiom in one call: partition equally, select ``rank``."""
     ds = ShardedDataset(dataset, make_rank_partition(world_size, compat=compat), compat=compat)
     return ds.select(rank_key(rank, world_size, compat=compat))
+
+
+def common_batches(base, world_size: int, batch_size: int, *, compat: bool = False, drop_last: bool = False) -> int:
+    """Batches per epoch that EVERY rank can run: the minimum over ranks of its shard's batch count.  Shards may differ
+    by a sample (60001 samples over 2 ranks), and then ``ceil(len/batch)`` can differ by one between ranks; each
+    training step is a collective, so the rank with the extra batch would wait for gradients nobody sends (the
+    reference hangs in that case, train.py:38/44).  Every rank can compute this from the shard table alone."""
+    counts = []
+    for r in range(world_size):
+        n = len(shard_for_rank(base, r, world_size, compat=compat and world_size > 1))
+        counts.append(n // batch_size if drop_last else -(-n // batch_size))
+    return min(counts)

@@ -102,8 +102,12 @@ class PinnedRingLoader:
     def __init__(self, images: torch.Tensor, targets: torch.Tensor, start: int, stop: int,
                  batch_size: int, spec: ImageSpec, *, shuffle: bool = True, fmt: str = "u8",
                  device: Optional[torch.device] = None, seed: int = 0, depth: int = 3,
-                 drop_last: bool = False):
+                 drop_last: bool = False, max_batches: Optional[int] = None):
+        """``max_batches`` caps the batches per epoch: every step of data-parallel training is a collective, so all
+        ranks must run the same number of steps even when their shards differ by a sample (see
+        :func:`b200dp.data.shard.common_batches`)."""
         assert fmt in ("u8", "f32")
+        self.max_batches = max_batches
         self.images, self.targets = images, targets
         self.start, self.stop = int(start), int(stop)
         self.batch_size = int(batch_size)
@@ -130,7 +134,8 @@ class PinnedRingLoader:
 
     def __len__(self) -> int:
         n = self.stop - self.start
-        return n // self.batch_size if self.drop_last else math.ceil(n / self.batch_size)
+        nb = n // self.batch_size if self.drop_last else math.ceil(n / self.batch_size)
+        return nb if self.max_batches is None else min(nb, self.max_batches)
 
     def _order(self) -> torch.Tensor:
         n = self.stop - self.start

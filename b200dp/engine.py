@@ -31,7 +31,7 @@ import torch
 import torch.distributed as dist
 
 from . import ckpt
-from .data.shard import shard_for_rank
+from .data.shard import common_batches, shard_for_rank
 from .data.synthetic import (CIFAR_SPEC, MNIST_SPEC, PinnedRingLoader, SyntheticImages,
                              normalise_reference)
 from .models.lenet import LeNet, LeNetConfig, loss_fn
@@ -47,10 +47,14 @@ class EagerStepper:
     name = "eager"
 
     def __init__(self, ctx: RankContext, cfg: LeNetConfig, hyper: OptHyper, *, loss_mode: str = "ref",
-                 spec=MNIST_SPEC, bucket_bytes: int = -1, overlap: bool = True):
+                 spec=MNIST_SPEC, bucket_bytes: int = -1, overlap: bool = True, comm: str = "torch",
+                 algo: str = "auto"):
+        """``comm="torch"``: gradients through ``torch.distributed`` (gloo / NCCL) + the flat torch optimizer;
+        ``comm="b200"``: torch-eager forward/backward, gradients and update through the fused sm_100a P2P kernels."""
         self.ctx, self.cfg, self.loss_mode, self.spec = ctx, cfg, loss_mode, spec
         model = LeNet(cfg).to(ctx.device)
-        self.ddp = DataParallel(model, hyper, bucket_bytes=bucket_bytes, overlap=overlap, device=ctx.device)
+        self.ddp = DataParallel(model, hyper, bucket_bytes=bucket_bytes, overlap=overlap, device=ctx.device,
+                                comm=comm, algo=algo)
         self.model = self.ddp.module
         self.optimizer = self.ddp.optimizer
         self._eval = torch.zeros(2, dtype=torch.float64, device=ctx.device)
@@ -85,6 +89,12 @@ class EagerStepper:
     def replica_divergence(self) -> float:
         return self.ddp.replica_divergence()
 
+    def error_flag(self) -> int:
+        return int(self.ddp.step_counter[2].item()) if self.ddp.native else 0
+
+    def close(self) -> None:
+        self.ddp.close()
+
 
 class Trainer:
     """Epoch loops around a stepper (reference ``train`` / ``test``)."""
@@ -110,6 +120,19 @@ class Trainer:
             return None
         return n_steps * batch * self.ctx.world_size / (now - prev)
 
+    def check_peers(self) -> None:
+        """Raise if the device's sticky error word is set: a peer did not deliver its gradients within the time bound
+        (csrc/ll_reduce.cu, csrc/reduce_update.cu) and this rank stopped updating its parameters.  Called where the
+        loop synchronises anyway — rank 0's log points and every rank's epoch end — so it costs one 4-byte read.  No
+        collective is needed for every rank to stop: the ranks that are still alive time out on the NEXT step's
+        gradients of whichever rank raised first.  The reference hangs in ``all_reduce`` here until NCCL's watchdog
+        fires (train.py:38)."""
+        st = self.stepper
+        if hasattr(st, "error_flag") and st.error_flag():
+            raise RuntimeError(
+                f"rank {self.ctx.rank}: a peer rank did not deliver its gradients within the time bound (dead or "
+                f"stalled rank?); training stopped at global step <= {self.global_step}")
+
     def _pump_for(self, loader):
         """The native step pump for (stepper, loader), when the combination supports it: native stepper with
         CUDA graphs, raw uint8 samples streamed to a CUDA device."""
@@ -131,7 +154,7 @@ class Trainer:
         order = loader._order().contiguous()
         loader.epoch += 1
         B, n_batches = loader.batch_size, len(loader)
-        n_full = (loader.stop - loader.start) // B
+        n_full = min((loader.stop - loader.start) // B, n_batches)
         run_ragged = n_full < n_batches
         if self.dry_run and n_full >= 1:                      # train.py:56-57: one batch only
             n_full, run_ragged = 1, False
@@ -144,6 +167,7 @@ class Trainer:
             self.global_step += n
             if self.ctx.is_main:
                 pump.wait_first()
+                self.check_peers()
                 last = float(self._loss_ring[c0])
                 self.log.print(train_line(epoch, c0, B, len(loader.dataset), n_batches, last))
                 first = self.global_step - n + 1
@@ -160,6 +184,7 @@ class Trainer:
                 last = float(loss.item())
                 self.log.print(train_line(epoch, n_full, len(x), len(loader.dataset), n_batches, last))
         pump.drain()
+        self.check_peers()
         return last
 
     def train_epoch(self, loader, epoch: int) -> Optional[float]:
@@ -173,12 +198,14 @@ class Trainer:
             self.global_step += 1
             if batch_idx % self.log_interval == 0 and self.ctx.is_main:
                 last = float(loss.item())  # the only host sync on the step path (train.py:55)
+                self.check_peers()
                 self.log.print(train_line(epoch, batch_idx, len(data), len(loader.dataset), n_batches, last))
                 self.log.event(kind="train", epoch=epoch, step=self.global_step, batch_idx=batch_idx, loss=last,
                                images_per_s=self._rate(self.global_step - self._steps_at_log, len(data)))
                 self._steps_at_log = self.global_step
             if self.dry_run:
                 break
+        self.check_peers()
         return last
 
     def test_epoch(self, loader) -> Tuple[float, int, int]:
@@ -208,9 +235,13 @@ def build_stepper(ctx: RankContext, args, cfg: LeNetConfig, hyper: OptHyper, spe
                              graph=not getattr(args, "no_graph", False),
                              overlap=not getattr(args, "no_overlap", False),
                              dtype=getattr(args, "dtype", "auto"))
+    # --eager: torch kernels for the model; the gradient path is still ours (--backend b200, default on GPU) unless
+    # --backend nccl/gloo asks for torch.distributed
+    comm = "b200" if (ctx.device.type == "cuda" and backend in (None, "b200")) else "torch"
     return EagerStepper(ctx, cfg, hyper, loss_mode=args.loss, spec=spec,
                         bucket_bytes=getattr(args, "bucket_bytes", -1),
-                        overlap=not getattr(args, "no_overlap", False))
+                        overlap=not getattr(args, "no_overlap", False), comm=comm,
+                        algo=getattr(args, "allreduce_algo", "auto"))
 
 
 def make_hyper(args) -> OptHyper:
@@ -235,10 +266,12 @@ def run(ctx: RankContext, args) -> dict:
 
     on_gpu = ctx.device.type == "cuda"
     fmt = "u8" if on_gpu else "f32"
-    mk = lambda base, sh: PinnedRingLoader(  # noqa: E731  (train.py:95-96: both loaders shuffle)
+    mk = lambda base, sh, cap: PinnedRingLoader(  # noqa: E731  (train.py:95-96: both loaders shuffle)
         base.images, base.targets, *sh.bounds(), per_rank_batch, spec, shuffle=True, fmt=fmt,
-        device=ctx.device if on_gpu else None, seed=args.seed + 17 * ctx.rank)
-    train_loader, test_loader = mk(base_train, tr), mk(base_test, te)
+        device=ctx.device if on_gpu else None, seed=args.seed + 17 * ctx.rank, max_batches=cap)
+    # every training step is a collective: all ranks run the batch count the smallest shard allows
+    train_cap = common_batches(base_train, ctx.world_size, per_rank_batch, compat=compat)
+    train_loader, test_loader = mk(base_train, tr, train_cap), mk(base_test, te, None)
 
     stepper = build_stepper(ctx, args, cfg, make_hyper(args), spec, per_rank_batch)
     scheduler = StepLR(stepper.optimizer, step_size=1, gamma=args.gamma)     # train.py:101

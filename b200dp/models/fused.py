@@ -304,13 +304,7 @@ class NativeStepper:
 
     # ---- optimizer scalars live on the device so graph replays see scheduler changes ----
     def _sync_hyper(self) -> None:
-        h = self.optimizer.hyper
-        if h.kind == "adadelta":
-            vec = (self.optimizer.lr, h.rho, h.eps, 0.0, h.weight_decay)
-        elif h.kind == "sgd":
-            vec = (self.optimizer.lr, h.momentum, 1.0 if h.nesterov else 0.0, 0.0, h.weight_decay)
-        else:
-            vec = (self.optimizer.lr, h.beta1, h.beta2, h.eps, h.weight_decay)
+        vec = self.optimizer.hyper_vector()
         if vec != self._hyper_cache:
             self.hyper_host[:5] = torch.tensor(vec, dtype=torch.float32)
             self.hyper_dev.copy_(self.hyper_host, non_blocking=True)

@@ -103,7 +103,6 @@ def load(build_if_missing: bool = True):
     lib.b200dp_symm_export.argtypes = [vp, C.c_char_p]
     lib.b200dp_symm_import.argtypes = [C.c_char_p, C.POINTER(vp)]
     lib.b200dp_symm_close.argtypes = [vp]
-    lib.b200dp_enable_peer_access.argtypes = [i]
     lib.b200dp_pump_create.argtypes = [C.POINTER(vp), C.POINTER(PumpDesc)]
     lib.b200dp_pump_run.argtypes = [vp, vp, i, vp]
     lib.b200dp_pump_wait_first.argtypes = [vp]

@@ -13,9 +13,11 @@ state:
 
 * :meth:`FlatOptimizer.step_torch` — a handful of fused torch ops over the
   whole arena; the CPU / gloo path and the oracle for the CUDA kernels;
-* the native kernels in ``csrc/update.cu`` / ``csrc/allreduce_update.cu``,
-  which apply the same arithmetic per element, fused with the cross-rank
-  gradient reduction (see :mod:`b200dp.parallel.ddp`).
+* the native kernels (``csrc/opt_math.cuh``, used by ``csrc/reduce_update.cu``
+  and ``csrc/ll_reduce.cu``), which apply the same arithmetic per element,
+  fused with the cross-rank gradient reduction; their ``hyper[]`` vector
+  ``{lr, h0, h1, h2, weight_decay}`` is built by :meth:`FlatOptimizer.hyper_vector`
+  (Adam's bias correction is computed on the device from the step number).
 
 The arithmetic follows torch.optim (single-tensor variants) exactly so that
 per-parameter torch optimizers and the flat one agree to fp32 round-off.
@@ -115,19 +117,14 @@ class FlatOptimizer:
             denom = (v.sqrt() / (bc2 ** 0.5)).add_(h.eps)
             p.addcdiv_(m, denom, value=-lr / bc1)
 
-    def kernel_scalars(self):
-        """(kind, lr, h0, h1, h2, h3) for the step about to be applied by a native
-        kernel; increments the step count (Adam bias correction is host-computed)."""
+    def hyper_vector(self):
+        """The kernels' ``hyper[]`` contract, ``(lr, h0, h1, h2, weight_decay)`` — include/b200dp.h."""
         h = self.hyper
-        self.step_count += 1
         if h.kind == "adadelta":
-            return OPT_ADADELTA, self.lr, h.rho, h.eps, h.weight_decay, 0.0
+            return (self.lr, h.rho, h.eps, 0.0, h.weight_decay)
         if h.kind == "sgd":
-            return OPT_SGD, self.lr, h.momentum, (1.0 if h.nesterov else 0.0), h.weight_decay, 0.0
-        bc1 = 1 - h.beta1 ** self.step_count
-        bc2 = 1 - h.beta2 ** self.step_count
-        # kernel: p -= (lr/bc1) * m / (sqrt(v)/sqrt(bc2) + eps)
-        return OPT_ADAM, self.lr / bc1, h.beta1, h.beta2, h.eps, 1.0 / (bc2 ** 0.5)
+            return (self.lr, h.momentum, 1.0 if h.nesterov else 0.0, 0.0, h.weight_decay)
+        return (self.lr, h.beta1, h.beta2, h.eps, h.weight_decay)
 
     # -- checkpointing -------------------------------------------------------
     def state_dict(self) -> Dict:

@@ -128,11 +128,3 @@ class FlatArena:
                 v.copy_(p.detach().to(device=device, dtype=torch.float32))
                 p.data = v
                 p.grad = self.layout.view(self.grad, name)
-
-    def bucket_views(self, flat: torch.Tensor) -> List[torch.Tensor]:
-        return [flat[b.start:b.stop] for b in self.layout.buckets]
-
-    def rebind_grads(self) -> None:
-        """Re-attach ``p.grad`` views (``zero_grad(set_to_none=True)`` detaches them)."""
-        for name, p in self.module.named_parameters():
-            p.grad = self.layout.view(self.grad, name)

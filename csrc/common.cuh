@@ -43,6 +43,23 @@ void set_last_error(const char* fmt, ...);
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE property of a kernel: a process that drives several GPUs
+// must set it once on each.  One DeviceOnce per launch site (a function-local static) remembers the devices done.
+struct DeviceOnce {
+    unsigned long long done[4] = {0ull, 0ull, 0ull, 0ull};     // bit per device ordinal, 0..255
+    template <class Kern>
+    cudaError_t max_dynamic_smem(Kern kern, int bytes) {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        const bool tracked = dev >= 0 && dev < 256;
+        if (tracked && ((__atomic_load_n(&done[dev >> 6], __ATOMIC_ACQUIRE) >> (dev & 63)) & 1ull)) return cudaSuccess;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);   // idempotent: a race only repeats it
+        if (e == cudaSuccess && tracked) __atomic_fetch_or(&done[dev >> 6], 1ull << (dev & 63), __ATOMIC_RELEASE);
+        return e;
+    }
+};
+
 template <class Kern, class Args>
 static inline cudaError_t launch_pdl(Kern kern, dim3 grid, dim3 block, size_t smem, cudaStream_t s, const Args& args) {
     cudaLaunchConfig_t cfg = {};

@@ -248,11 +248,8 @@ extern "C" int b200dp_conv_bwd(const void* x, int in_is_u8, float mean, float st
     ConvBwdArgs a{x, in_is_u8, d.in_hw, mean, std, p1, idx1, p2, d.ld_p2 > 0 ? d.ld_p2 : 400, idx2, dp2, w2, partials, partial_stride,
                   off_w1, off_b1, off_w2, off_b2, d.batch};
     auto kern = conv_bwd_kernel<1, 6, 16>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        B200DP_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
-        attr_done = true;
-    }
+    static DeviceOnce attr;
+    B200DP_CHECK(attr.max_dynamic_smem(kern, (int)C::SMEM));
     B200DP_CHECK(launch_pdl(kern, dim3(num_partials_for(d.batch)), dim3(CB_NT), C::SMEM, (cudaStream_t)s, a));
     B200DP_CHECK(cudaGetLastError());
     return 0;
@@ -305,15 +302,17 @@ static int noalloc_device_setup(float** rows_out) {
     int dev = -1;
     B200DP_CHECK(cudaGetDevice(&dev));
     B200DP_REQUIRE(dev >= 0 && dev < NA_MAX_DEVICES, "device ordinal beyond the per-device table");
-    if (g_rows_addr[dev] == nullptr) {
+    float* cached = __atomic_load_n(&g_rows_addr[dev], __ATOMIC_ACQUIRE);
+    if (cached == nullptr) {
         float* p = nullptr;
         B200DP_CHECK(cudaGetSymbolAddress((void**)&p, g_conv_bwd_rows));
         B200DP_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
         B200DP_CHECK(cudaFuncSetAttribute(conv_bwd_kernel<1, 6, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)ConvBwdCfg<1, 6, 16>::SMEM));
-        g_rows_addr[dev] = p;
+        __atomic_store_n(&g_rows_addr[dev], p, __ATOMIC_RELEASE);   // two racing first calls store the same address
+        cached = p;
     }
-    *rows_out = g_rows_addr[dev];
+    *rows_out = cached;
     return 0;
 }
 

@@ -141,11 +141,8 @@ static int launch_conv_fwd(const ConvFwdArgs& a, cudaStream_t s) {
     using C = ConvFwdCfg<CIN, COUT, IN_W, OCT, GPB, IPB, FIRST>;
     auto kern = conv5_pool_fwd_kernel<CIN, COUT, IN_W, OCT, GPB, IPB, FIRST>;
     const size_t smem = C::SMEM_FLOATS * sizeof(float);
-    static bool attr_done = false;  // per-instantiation; the attribute is per-function, process-wide per device
-    if (smem > 48 * 1024 && !attr_done) {
-        B200DP_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_done = true;
-    }
+    static DeviceOnce attr;         // one per kernel instantiation
+    if (smem > 48 * 1024) B200DP_CHECK(attr.max_dynamic_smem(kern, (int)smem));
     dim3 grid((a.B + IPB - 1) / IPB, COUT / C::COUT_BLK);
     B200DP_CHECK(launch_pdl(kern, dim3(grid), dim3(C::NT), smem, s, a));
     B200DP_CHECK(cudaGetLastError());

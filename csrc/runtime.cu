@@ -59,14 +59,3 @@ extern "C" int b200dp_symm_close(void* imported_ptr) {
     B200DP_CHECK(cudaIpcCloseMemHandle(imported_ptr));
     return 0;
 }
-extern "C" int b200dp_enable_peer_access(int peer_device) {
-    int can = 0, dev = 0;
-    B200DP_CHECK(cudaGetDevice(&dev));
-    if (peer_device == dev) return 0;
-    B200DP_CHECK(cudaDeviceCanAccessPeer(&can, dev, peer_device));
-    B200DP_REQUIRE(can == 1, "peer access not possible between these devices");
-    cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
-    if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return 0; }
-    B200DP_CHECK(e);
-    return 0;
-}

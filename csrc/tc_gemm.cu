@@ -456,11 +456,8 @@ static int tc_launch(const b200dp_tc_problem* probs, int count, bool retile, flo
         p.tickets = tickets ? tickets + pl.tk_off[i] : nullptr;
         total += pl.tiles[i] * pl.splits[i];
     }
-    static bool attr_done = false;
-    if (!attr_done) {
-        B200DP_CHECK(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
-        attr_done = true;
-    }
+    static DeviceOnce attr;
+    B200DP_CHECK(attr.max_dynamic_smem(tc_gemm_kernel, TC_SMEM));
     B200DP_CHECK(launch_pdl(tc_gemm_kernel, dim3(total), dim3(TC_THREADS), TC_SMEM, (cudaStream_t)s, g));
     B200DP_CHECK(cudaGetLastError());
     return 0;

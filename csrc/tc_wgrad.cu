@@ -281,11 +281,8 @@ template <int LAYER, int CIN, int COUT>
 static int wg_launch(const WgArgs& a, int rows, cudaStream_t s) {
     using C = WgCfg<LAYER, CIN, COUT>;
     auto kern = wg_conv_kernel<LAYER, CIN, COUT>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        B200DP_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
-        attr_set = true;
-    }
+    static DeviceOnce attr;            // one per kernel instantiation, tracks the devices already set up
+    B200DP_CHECK(attr.max_dynamic_smem(kern, (int)C::SMEM));
     WgArgs b = a;
     b.dbg = g_wg_dbg;
     B200DP_CHECK(launch_pdl(kern, dim3(rows), dim3(WG_THREADS), C::SMEM, s, b));

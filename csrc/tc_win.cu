@@ -391,11 +391,8 @@ template <int KIND, int CIN, int COUT>
 static int win_launch(const WinArgs& a, cudaStream_t s) {
     using C = WinCfg<KIND, CIN, COUT>;
     auto kern = win_conv_kernel<KIND, CIN, COUT>;
-    static bool attr_set = false;      // per kernel instantiation; setting it again is harmless
-    if (!attr_set) {
-        B200DP_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
-        attr_set = true;
-    }
+    static DeviceOnce attr;            // one per kernel instantiation, tracks the devices already set up
+    B200DP_CHECK(attr.max_dynamic_smem(kern, (int)C::SMEM));
     WinArgs b = a;
     b.dbg = g_win_dbg;
     B200DP_CHECK(launch_pdl(kern, dim3((a.B + C::G - 1) / C::G), dim3(WIN_THREADS), C::SMEM, s, b));

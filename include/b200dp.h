@@ -277,7 +277,6 @@ int b200dp_symm_free(void* ptr);
 int b200dp_symm_export(void* ptr, uint8_t handle_out[64]);
 int b200dp_symm_import(const uint8_t handle[64], void** ptr_out);
 int b200dp_symm_close(void* imported_ptr);
-int b200dp_enable_peer_access(int peer_device);
 
 /* ---- native step pump (csrc/pump.cu) ---------------------------------------
  * The host side of the hot loop in C++: replaces the DataLoader iteration, the two .cuda()
