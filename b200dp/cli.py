@@ -48,6 +48,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--loss", choices=["ref", "xent"], default="ref",
                    help="ref = nll_loss on softmax probabilities like the reference; xent = cross-entropy")
     p.add_argument("--dataset", choices=["mnist", "cifar"], default="mnist", help="synthetic data shape")
+    p.add_argument("--data-root", default=None,
+                   help="directory with the MNIST IDX files (torchvision layout <root>/MNIST/raw or flat; .gz accepted) "
+                        "or train.npz/test.npz dumps; the reference reads ./data (train.py:88).  Absent: synthetic data")
     p.add_argument("--train-size", type=int, default=60000)
     p.add_argument("--test-size", type=int, default=10000)
     p.add_argument("--width-mult", type=int, default=1)

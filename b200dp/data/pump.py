@@ -25,8 +25,9 @@ class StepPump:
     captured for the full batch): feed them to ``stepper.train_step``."""
 
     def __init__(self, stepper, images: torch.Tensor, targets: torch.Tensor, batch: int, *, depth: int = 3):
-        assert not images.is_cuda and images.is_contiguous() and images.dtype == torch.uint8, \
-            "the pump streams raw uint8 samples (the first kernel normalises on the device)"
+        assert not images.is_cuda and images.is_contiguous() and images.dtype in (torch.uint8, torch.float32), \
+            "the pump streams raw uint8 samples (the first kernel normalises on the device) or float32 samples that " \
+            "are already transformed"
         assert targets.dtype == torch.int64 and targets.is_contiguous()
         assert 2 <= depth <= 8
         self.stepper, self.images, self.targets = stepper, images, targets
@@ -34,11 +35,11 @@ class StepPump:
         assert self.batch == stepper.net.B, "the pump runs the stepper's full batch"
         dev = stepper.device
         shape = (self.batch,) + tuple(images.shape[1:])
-        self.host_x = [torch.empty(shape, dtype=torch.uint8).pin_memory() for _ in range(depth)]
+        self.host_x = [torch.empty(shape, dtype=images.dtype).pin_memory() for _ in range(depth)]
         self.host_y = [torch.empty(self.batch, dtype=torch.int64).pin_memory() for _ in range(depth)]
-        self.dev_x = [torch.empty(shape, dtype=torch.uint8, device=dev) for _ in range(depth)]
+        self.dev_x = [torch.empty(shape, dtype=images.dtype, device=dev) for _ in range(depth)]
         self.dev_y = [torch.empty(self.batch, dtype=torch.int64, device=dev) for _ in range(depth)]
-        self.h2d_bytes_per_step = self.host_x[0].numel() + 8 * self.batch
+        self.h2d_bytes_per_step = self.host_x[0].numel() * images.element_size() + 8 * self.batch
         self._graphs = []
         self._handle: Optional[int] = None
         self._loss_keepalive = None
@@ -68,7 +69,7 @@ class StepPump:
             self._graphs.append(g)
         d = native.PumpDesc()
         d.images, d.targets = self.images.data_ptr(), self.targets.data_ptr()
-        d.image_bytes = self.images[0].numel()
+        d.image_bytes = self.images[0].numel() * self.images.element_size()
         d.batch, d.depth = self.batch, self.depth
         for s in range(self.depth):
             d.host_x[s], d.host_y[s] = self.host_x[s].data_ptr(), self.host_y[s].data_ptr()

@@ -94,9 +94,11 @@ class PinnedRingLoader:
 
     ``images``/``targets`` are the *base* tensors; ``start``/``stop`` delimit
     this rank's contiguous shard (see :class:`b200dp.data.shard.ShardedDataset`).
-    ``fmt`` is ``"u8"`` (raw bytes; device normalises) or ``"f32"`` (host
-    normalises like the reference).  With ``device=None`` the loader yields the
-    pinned host tensors themselves (CPU / gloo path).
+    ``fmt`` is ``"u8"`` (raw bytes; device normalises), ``"f32"`` (host
+    normalises like the reference) or ``"pre"`` (the base array already holds
+    transformed float32 samples — any user ``Dataset``, see
+    :meth:`from_dataset`).  With ``device=None`` the loader yields the pinned
+    host tensors themselves (CPU / gloo path).
     """
 
     def __init__(self, images: torch.Tensor, targets: torch.Tensor, start: int, stop: int,
@@ -106,7 +108,8 @@ class PinnedRingLoader:
         """``max_batches`` caps the batches per epoch: every step of data-parallel training is a collective, so all
         ranks must run the same number of steps even when their shards differ by a sample (see
         :func:`b200dp.data.shard.common_batches`)."""
-        assert fmt in ("u8", "f32")
+        assert fmt in ("u8", "f32", "pre")
+        assert (images.dtype == torch.float32) == (fmt == "pre"), "fmt 'pre' <=> float32 base array"
         self.max_batches = max_batches
         self.images, self.targets = images, targets
         self.start, self.stop = int(start), int(stop)
@@ -132,6 +135,25 @@ class PinnedRingLoader:
             self._consumed = [None] * depth
         self.h2d_bytes_per_batch = int(np.prod(shape)) * (1 if fmt == "u8" else 4) + self.batch_size * 8
 
+    @classmethod
+    def from_dataset(cls, dataset, batch_size: int, spec: ImageSpec, *, host_normalise: bool = False, workers: int = 4,
+                     **kw) -> "PinnedRingLoader":
+        """The loader over ANY map-style dataset — the reference's ``DataLoader(SplitDataset(...))`` (train.py:88-96).
+        A :class:`~b200dp.data.shard.ShardedDataset` contributes its shard bounds and its base dataset; the base is
+        materialised once into host arrays (:func:`b200dp.data.files.materialise`: zero-copy for datasets that expose
+        uint8 storage, one ``__getitem__`` sweep on a thread pool otherwise)."""
+        from .files import materialise
+        from .shard import ShardedDataset
+        if isinstance(dataset, ShardedDataset):
+            start, stop = dataset.bounds()
+            base = dataset.dataset
+        else:
+            start, stop, base = 0, len(dataset), dataset
+        images, targets, fmt = materialise(base, spec, workers=workers)
+        if fmt == "u8" and host_normalise:
+            fmt = "f32"
+        return cls(images, targets, start, stop, batch_size, spec, fmt=fmt, **kw)
+
     def __len__(self) -> int:
         n = self.stop - self.start
         nb = n // self.batch_size if self.drop_last else math.ceil(n / self.batch_size)
@@ -147,7 +169,7 @@ class PinnedRingLoader:
     def _stage(self, slot: int, idx: torch.Tensor) -> int:
         b = idx.numel()
         hx, hy = self._host_x[slot][:b], self._host_y[slot][:b]
-        if self.fmt == "u8":
+        if self.fmt in ("u8", "pre"):
             torch.index_select(self.images, 0, idx, out=hx)
         else:
             hx.copy_(normalise_reference(self.images.index_select(0, idx), self.spec))

@@ -139,7 +139,7 @@ class Trainer:
         st = self.stepper
         if not (hasattr(st, "make_pump") and getattr(st, "use_graph", False) and not self.no_pump):
             return None
-        if not (isinstance(loader, PinnedRingLoader) and loader.fmt == "u8" and loader.device is not None
+        if not (isinstance(loader, PinnedRingLoader) and loader.fmt in ("u8", "pre") and loader.device is not None
                 and loader.device.type == "cuda" and loader.batch_size == st.net.B):
             return None
         key = id(loader)
@@ -249,6 +249,24 @@ def make_hyper(args) -> OptHyper:
                     weight_decay=getattr(args, "weight_decay", 0.0))
 
 
+def load_datasets(args, spec):
+    """The train / test base datasets: real files under ``--data-root`` when they are there (the reference reads
+    torchvision MNIST from ``./data``, train.py:88-93; no download here), else synthetic data of the same shape."""
+    import os
+    from .data.files import MNISTFiles, find_mnist, load_arrays
+    root = getattr(args, "data_root", None)
+    if root:
+        npz = [os.path.join(root, f"{s}.npz") for s in ("train", "test")]
+        if all(os.path.isfile(f) for f in npz):
+            return load_arrays(npz[0], spec), load_arrays(npz[1], spec), f"{npz[0]}, {npz[1]}"
+        if args.dataset == "mnist" and find_mnist(root, True) and find_mnist(root, False):
+            tr, te = MNISTFiles(root, True, spec), MNISTFiles(root, False, spec)
+            return tr, te, f"MNIST IDX files {tr.paths[0]} ({len(tr)} train / {len(te)} test samples)"
+    note = f"synthetic {args.dataset}-shaped data" + (f" (no dataset files under {root!r})" if root else "")
+    return (SyntheticImages(args.train_size, spec, seed=args.seed * 7919 + 1),
+            SyntheticImages(args.test_size, spec, seed=args.seed * 7919 + 2), note)
+
+
 def run(ctx: RankContext, args) -> dict:
     """Per-rank entry (reference ``run(rank, size, args)``, train.py:79-108)."""
     torch.manual_seed(args.seed)                      # train.py:80 — same seed on every rank
@@ -258,8 +276,9 @@ def run(ctx: RankContext, args) -> dict:
 
     spec = MNIST_SPEC if args.dataset == "mnist" else CIFAR_SPEC
     cfg = LeNetConfig(in_ch=spec.channels, width_mult=args.width_mult, in_hw=spec.height)
-    base_train = SyntheticImages(args.train_size, spec, seed=args.seed * 7919 + 1)
-    base_test = SyntheticImages(args.test_size, spec, seed=args.seed * 7919 + 2)
+    base_train, base_test, source = load_datasets(args, spec)
+    if ctx.is_main and getattr(args, "data_root", None):
+        print(f"data: {source}")
     compat = getattr(args, "compat_shard", False)
     tr = shard_for_rank(base_train, ctx.rank, ctx.world_size, compat=compat and ctx.world_size > 1)
     te = shard_for_rank(base_test, ctx.rank, ctx.world_size, compat=compat and ctx.world_size > 1)
