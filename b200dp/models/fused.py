@@ -47,7 +47,7 @@ class NativeLeNet:
 
     def __init__(self, cfg: LeNetConfig, batch: int, device: torch.device, *, loss_mode: str = "ref",
                  spec: ImageSpec = MNIST_SPEC, module: Optional[LeNet] = None, tc: bool = False,
-                 conv_tc=None):
+                 conv_tc=None, head_fused: Optional[bool] = None):
         """``tc=True`` routes the five GEMM-shaped layers (conv3, FC.0 and their backward, FC.2's weight
         gradient) through the tcgen05/TMEM/TMA tf32 kernel; ``tc=False`` keeps them in exact fp32 on CUDA cores.
         ``conv_tc`` does the same for the two 5x5 convolutions (window-tile bf16 tcgen05 kernels): ``True`` / ``False``
@@ -70,6 +70,10 @@ class NativeLeNet:
         if cfg.width_mult > 1 and not self.convbwd_tc:
             raise ValueError("the wide model's convolution backward runs on the tensor-core kernels only")
         self.loss_mode = _LOSS_MODES[loss_mode]
+        # conv3 + FC.0 + FC.2 + loss + the row-local backward in ONE fp32 launch (csrc/head_fused.cu) where the layer
+        # widths allow it (the reference geometry); the dense layers of the wide model stay separate GEMM launches
+        fits = native.head_fused_supported(cfg.c2 * 25, cfg.c3, cfg.f1, cfg.num_classes)
+        self.head_fused = fits if head_fused is None else (bool(head_fused) and fits)
         self.module = module if module is not None else LeNet(cfg)
         self.module.to(self.device)
         names = [n for n, _ in self.module.named_parameters()]
@@ -124,7 +128,10 @@ class NativeLeNet:
                                   ("ConvNet.1.weight", "ConvNet.1.bias", "ConvNet.4.weight", "ConvNet.4.bias"))
         self.launches_per_step = 0
         self.gemm_ws = native.GemmWorkspace(self.device) if self.tc else None
-        self.pack_stream = torch.cuda.Stream(device=self.device) if (self.conv_tc and not self.conv1_tc) else None
+        # second stream for work that does not sit on the step's dependency chain: the weight pack beside the first
+        # layer, conv2's weight gradient beside conv2's data gradient
+        self.pack_stream = torch.cuda.Stream(device=self.device) if self.conv_tc else None
+        self.parallel_wgrad = True
 
     def dims(self, b: int) -> native.Dims:
         c = self.cfg
@@ -137,7 +144,7 @@ class NativeLeNet:
         d, w = self.dims(b), self.w
         need_pack = self.conv1_tc or self.conv2_tc or (self.convbwd_tc and train)
         fork = None
-        if need_pack and not self.conv1_tc and self.pack_stream is not None:
+        if need_pack and not self.conv1_tc:
             # the first layer runs on CUDA cores and needs no packed panels: pack beside it
             main = torch.cuda.current_stream(self.device)
             self.pack_stream.wait_stream(main)
@@ -160,6 +167,13 @@ class NativeLeNet:
             native.conv2_fwd(self.p1, w["ConvNet.4.weight"], w["ConvNet.4.bias"], self.p2, self.idx2 if train else None, d)
         c = self.cfg
         k3 = c.c2 * 25
+        if self.head_fused:
+            native.head_fused(self.p2, self.ld_p2, w["ConvNet.7.weight"], w["ConvNet.7.bias"], w["FC.0.weight"],
+                              w["FC.0.bias"], w["FC.2.weight"], w["FC.2.bias"], y, self.loss_mode, self.a3, self.ld_a3,
+                              self.h1, self.ld_h1, self.probs, self.loss_rows, self.loss,
+                              self.dlogits if train else None, self.ld_dl, self.dz1 if train else None,
+                              self.dz3 if train else None, None if train else self.eval_acc, self.ticket, b)
+            return
         if self.tc:
             T = native.tc_problem
             native.tc_gemm_group([T(self.p2, self.ld_p2, False, w["ConvNet.7.weight"], k3, False, b, c.c3, k3,
@@ -180,7 +194,30 @@ class NativeLeNet:
         b, c, w, g = x.shape[0], self.cfg, self.w, self.g
         d = self.dims(b)
         k3 = c.c2 * 25
-        if self.tc:
+        if self.head_fused:
+            # dz3 came out of the fused head: the four remaining products depend on its outputs only -> one launch
+            if self.tc:
+                T, nc = native.tc_problem, c.num_classes
+                native.tc_gemm_group([
+                    T(self.dlogits, self.ld_dl, True, self.h1, self.ld_h1, True, nc, c.f1 + 1, b,
+                      out=g["FC.2.weight"], ld_out=c.f1, colext=g["FC.2.bias"]),
+                    T(self.dz1, c.f1, True, self.a3, self.ld_a3, True, c.f1, c.c3 + 1, b,
+                      out=g["FC.0.weight"], ld_out=c.c3, colext=g["FC.0.bias"]),
+                    T(self.dz3, c.c3, True, self.p2, self.ld_p2, True, c.c3, k3 + 1, b,
+                      out=g["ConvNet.7.weight"], ld_out=k3, colext=g["ConvNet.7.bias"]),
+                    T(self.dz3, c.c3, False, w["ConvNet.7.weight"], k3, True, b, k3, c.c3, out=self.dp2, ld_out=k3),
+                ], self.gemm_ws)
+            else:
+                native.linear_bwd_group([
+                    native.bwd_problem(1, self.dlogits, self.h1, None, g["FC.2.weight"], g["FC.2.bias"], b, c.num_classes, c.f1),
+                    native.bwd_problem(1, self.dz1, self.a3, None, g["FC.0.weight"], g["FC.0.bias"], b, c.f1, c.c3),
+                    native.bwd_problem(1, self.dz3, self.p2, None, g["ConvNet.7.weight"], g["ConvNet.7.bias"], b, c.c3, k3),
+                    native.bwd_problem(0, self.dz3, w["ConvNet.7.weight"], None, self.dp2, None, b, c.c3, k3),
+                ])
+            if on_bucket:
+                on_bucket(0)
+                on_bucket(1)
+        elif self.tc:
             T, nc = native.tc_problem, c.num_classes
             native.tc_gemm_group([
                 # dW fc2 = dlogits^T h1 (+db through h1's ones column)
@@ -222,11 +259,23 @@ class NativeLeNet:
         self.cur_partials = self._num_partials(d)
         if self.convbwd_tc:
             ld_p2 = self.ld_p2 or k3
+            # conv2's weight gradient needs dp2 only; conv1's needs conv2's data gradient g1: the former runs beside
+            # the dgrad on the second stream (disjoint columns of the partial rows)
+            main = torch.cuda.current_stream(self.device)
+            par = self.parallel_wgrad and self.pack_stream is not None
+            if par:
+                self.pack_stream.wait_stream(main)
+                with torch.cuda.stream(self.pack_stream):
+                    native.tcw_conv_wgrad(2, self.p1, 0.0, 1.0, self.dp2, self.p2, ld_p2, self.idx2, self.partials,
+                                          self.partial_stride, ow2, ob2, d)
             native.tcw_conv2_dgrad(self.dp2, self.p2, self.idx2, self.wpack, self.p1, self.g1, d)
-            native.tcw_conv_wgrad(2, self.p1, 0.0, 1.0, self.dp2, self.p2, ld_p2, self.idx2, self.partials,
-                                  self.partial_stride, ow2, ob2, d)
+            if not par:
+                native.tcw_conv_wgrad(2, self.p1, 0.0, 1.0, self.dp2, self.p2, ld_p2, self.idx2, self.partials,
+                                      self.partial_stride, ow2, ob2, d)
             native.tcw_conv_wgrad(1, x, self.spec.mean, self.spec.std, self.g1, None, 0, self.idx1, self.partials,
                                   self.partial_stride, ow1, ob1, d)
+            if par:
+                main.wait_stream(self.pack_stream)
         else:
             native.conv_bwd(x, self.spec.mean, self.spec.std, self.p1, self.idx1, self.p2, self.idx2, self.dp2,
                             w["ConvNet.4.weight"], self.partials, self.partial_stride, ow1, ob1, ow2, ob2, d)
@@ -264,7 +313,9 @@ class NativeStepper:
             # faster on CUDA cores, everything from the second layer on is faster on the tensor cores
             conv = "tc" if wide else ("simt" if dtype == "fp32" else "hybrid")
         if dtype == "auto":
-            dtype = "tf32" if wide else "fp32"      # dense layers: tcgen05 wins from the wide model's sizes on
+            # dense layers: with the fused fp32 head (conv3 + FC.0 + FC.2 forward, one launch) the only GEMM launch left
+            # is the backward group {dW FC.2, dW FC.0, dW conv3, dP2}, which is faster on tcgen05 (tf32) at both sizes
+            dtype = "tf32"
         self.dtype = "fp32" if dtype == "fp32" else "tf32"       # GEMM operand type
         self.conv_mode = conv
         conv_tc = {"simt": False, "tc": True, "hybrid": (False, True, True)}[conv]
@@ -298,9 +349,11 @@ class NativeStepper:
         self._warm = 0
         self._comm_off = False        # measurement aid: see set_comm_enabled
         self._pumps = []
-        n = 5 + (1 if self.net.conv_tc else 0) + 2 + (3 if self.net.convbwd_tc else 1)     # forward, GEMM backward, conv backward
-        n += (1 + (2 if self.world > 1 else 0)) if self.fused_final else 3                 # reduce/update (+ pushes)
-        self.launches_per_step = n
+        hf = self.net.head_fused
+        n = (3 if hf else 5) + (1 if self.net.conv_tc else 0) + (1 if hf else 2) + (3 if self.net.convbwd_tc else 1)
+        pushes = 0 if self.world == 1 else (1 if hf else 2)
+        n += (1 + pushes) if self.fused_final else 3                                       # reduce/update (+ pushes)
+        self.launches_per_step = n            # forward + GEMM backward + conv backward + gradient exchange/update
 
     # ---- optimizer scalars live on the device so graph replays see scheduler changes ----
     def _sync_hyper(self) -> None:
@@ -334,6 +387,11 @@ class NativeStepper:
             b = self.arena.layout.buckets[bucket_index]
             native.grad_push(self.arena.grad, b.start, b.numel, self.step_counter, cs)
 
+    def _push_range(self, start: int, count: int) -> None:
+        cs = self._comm_struct(0, False)
+        if cs is not None:
+            native.grad_push(self.arena.grad, start, count, self.step_counter, cs)
+
     def _final_update(self, pushed: bool) -> None:
         """Push protocol: the step's single wait + sum + average + update launch over the whole arena; it sums the
         convolution backward's partial rows and pushes that bucket itself."""
@@ -349,9 +407,14 @@ class NativeStepper:
         self.net.forward(x, y, train=True)
         side = self.side
 
+        bk = self.arena.layout.buckets
+        both = self.net.head_fused and bk[1].stop == bk[0].start     # the two dense buckets finish in one launch
+
         def on_bucket(i: int) -> None:
             if self.fused_final:
                 last = i == 2
+                if both and i == 0:
+                    return                           # sent together with bucket 1 (adjacent in the arena)
                 if side is None:                     # no overlap: everything after backward, in one launch
                     if last:
                         self._final_update(pushed=False)
@@ -362,6 +425,8 @@ class NativeStepper:
                 with torch.cuda.stream(side):
                     if last:
                         self._final_update(pushed=True)
+                    elif both:
+                        self._push_range(bk[1].start, bk[0].stop - bk[1].start)
                     else:
                         self._push(i)
                 return

@@ -77,6 +77,11 @@ def load(build_if_missing: bool = True):
     lib.b200dp_conv2_fwd.argtypes = [vp, vp, vp, vp, vp, Dims, vp]
     lib.b200dp_linear_fwd.argtypes = [vp, vp, vp, vp, i, i, i, i, vp]
     lib.b200dp_head_tail.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, vp]
+    lib.b200dp_head_fused_supported.argtypes = [i, i, i, i]
+    lib.b200dp_head_fused_set_debug.argtypes = [vp]
+    lib.b200dp_head_fused_set_debug.restype = None
+    lib.b200dp_head_fused.argtypes = [vp, i, vp, vp, vp, vp, vp, vp, vp, i, vp, i, vp, i, vp, vp, vp, vp, i, vp, vp, vp, vp,
+                                      i, i, i, i, i, vp]
     lib.b200dp_linear_bwd_group.argtypes = [C.POINTER(BwdProblem), i, vp]
     lib.b200dp_tc_gemm_group.argtypes = [C.POINTER(TcProblem), i, vp]
     lib.b200dp_tc_gemm_group_splitk.argtypes = [C.POINTER(TcProblem), i, vp, C.c_long, vp, i, vp]
@@ -206,6 +211,21 @@ def head_tail(h1, w, b, target, loss_mode: int, probs, loss_rows, loss_out, dlog
     check(load().b200dp_head_tail(_p(h1), _p(w), _p(b), _p(target), loss_mode, _p(probs), _p(loss_rows),
                                   _p(loss_out), _p(dlogits), _p(dz1), _p(eval_acc), _p(ticket), B, F1,
                                   w.shape[0], ld_h1, ld_dlogits, _stream()), "head_tail")
+
+
+def head_fused_supported(K3: int, C3: int, F1: int, ncls: int) -> bool:
+    return bool(load().b200dp_head_fused_supported(K3, C3, F1, ncls))
+
+
+def head_fused(p2, ld_p2: int, w3, b3, w1, b1, w2, b2, target, loss_mode: int, a3, ld_a3: int, h1, ld_h1: int, probs,
+               loss_rows, loss_out, dlogits, ld_dlogits: int, dz1, dz3, eval_acc, ticket, B: int) -> None:
+    """conv3 + FC.0 + FC.2 + softmax + loss (+ dlogits, dz1, dz3 when training) in one launch (csrc/head_fused.cu)."""
+    C3, K3 = w3.shape[0], w3.numel() // w3.shape[0]
+    F1, ncls = w1.shape[0], w2.shape[0]
+    check(load().b200dp_head_fused(_p(p2), ld_p2, _p(w3), _p(b3), _p(w1), _p(b1), _p(w2), _p(b2), _p(target), loss_mode,
+                                   _p(a3), ld_a3, _p(h1), ld_h1, _p(probs), _p(loss_rows), _p(loss_out), _p(dlogits),
+                                   ld_dlogits, _p(dz1), _p(dz3), _p(eval_acc), _p(ticket), B, K3, C3, F1, ncls, _stream()),
+          "head_fused")
 
 
 # ---- backward ----------------------------------------------------------------

@@ -70,6 +70,24 @@ int b200dp_head_tail(const float* h1, const float* w, const float* b, const int6
                      double* eval_acc, int* ticket, int B, int F1, int ncls, int ld_h1, int ld_dlogits,
                      b200dp_stream_t s);
 
+/* Fused head (csrc/head_fused.cu), one launch, exact fp32: conv3 (GEMM on the 5x5 map) + LeakyReLU -> FC.0 + LeakyReLU
+ * -> FC.2 -> softmax -> loss (+ eval counters), and in training the row-local backward: dlogits,
+ * dz1 = (dlogits W2) * leaky'(h1), dz3 = (dz1 W1) * leaky'(a3).  A CTA carries 4 batch rows through the whole chain
+ * in shared memory.  Replaces cnn.py:16-17, 20-23, train.py:48 and the row-local half of their backward (train.py:49);
+ * equivalent to b200dp_linear_fwd x2 + b200dp_head_tail + the kind-0 problem of b200dp_linear_bwd_group that produces
+ * dz3.  What remains for the backward GEMM launch: dW FC.2, dW FC.0, dW conv3, dP2.
+ * p2: [B][ld_p2] (K3 = c2*25 valid columns), a3: [B][ld_a3], h1: [B][ld_h1], dlogits: [B][ld_dlogits] (pitches 0 =
+ * dense), dz1: [B][F1], dz3: [B][C3] dense.  dlogits / dz1 / dz3 all NULL = evaluation.  Other arguments as
+ * b200dp_head_tail.  Limits: C3, F1 <= 128, ncls <= 16 (b200dp_head_fused_supported). */
+int b200dp_head_fused_supported(int K3, int C3, int F1, int ncls);
+/* Profiling aid: while dbg != NULL, CTA 0 of every fused-head launch stores clock64() stamps of its phases in dbg[0..16). */
+void b200dp_head_fused_set_debug(long long* dbg);
+int b200dp_head_fused(const float* p2, int ld_p2, const float* w3, const float* b3, const float* w1, const float* b1,
+                      const float* w2, const float* b2, const int64_t* target, int loss_mode, float* a3, int ld_a3,
+                      float* h1, int ld_h1, float* probs, float* loss_rows, float* loss_out, float* dlogits,
+                      int ld_dlogits, float* dz1, float* dz3, double* eval_acc, int* ticket, int B, int K3, int C3,
+                      int F1, int ncls, b200dp_stream_t s);
+
 /* ---- backward ------------------------------------------------------------
  * Up to four independent GEMM-shaped backward problems in ONE launch.
  * kind 0: dX[M][K] = (dY[M][N] W[N][K]) * leaky'(act_prev[M][K])   (act_prev nullable)

@@ -139,6 +139,68 @@ def test_head_tail(mode, B, F1):
     assert int(acc[1]) == int(probs.argmax(1).eq(t).sum())
 
 
+@pytest.mark.parametrize("mode", ["ref", "xent"])
+@pytest.mark.parametrize("B,K3,C3,F1,pitched", [(256, 400, 120, 84, False), (37, 400, 120, 84, True), (64, 150, 128, 128, True),
+                                                  (9, 33, 17, 5, False)])
+def test_head_fused(mode, B, K3, C3, F1, pitched):
+    """conv3 + FC.0 + FC.2 + softmax + loss + dlogits + dz1 + dz3 in one launch against fp64 autograd (cnn.py:16-23,
+    train.py:48-49), dense and pitched buffers, ragged row blocks, eval counters."""
+    native = _native()
+    torch.manual_seed(5)
+    dev = "cuda"
+    d64 = dict(device=dev, dtype=torch.float64)
+    p2 = torch.randn(B, K3, **d64)
+    w3, b3 = torch.randn(C3, K3, **d64) / K3 ** 0.5, torch.randn(C3, **d64) * 0.1
+    w1, b1 = torch.randn(F1, C3, **d64) / C3 ** 0.5, torch.randn(F1, **d64) * 0.1
+    w2, b2 = torch.randn(10, F1, **d64) / F1 ** 0.5, torch.randn(10, **d64) * 0.1
+    t = torch.randint(0, 10, (B,), device=dev)
+    z3 = F.linear(p2, w3, b3).requires_grad_(True)
+    z3.retain_grad()
+    a3 = F.leaky_relu(z3, 0.2)
+    z1 = F.linear(a3, w1, b1)
+    z1.retain_grad()
+    h1 = F.leaky_relu(z1, 0.2)
+    logits = F.linear(h1, w2, b2)
+    logits.retain_grad()
+    probs = logits.softmax(-1)
+    loss = loss_fn(probs if mode == "ref" else logits, t, mode)
+    loss.backward()
+
+    f = lambda a: a.detach().float().contiguous()  # noqa: E731
+    pad = 4 if pitched else 0
+    ld_p2, ld_a3, ld_h1, ld_dl = K3 + pad, C3 + pad, F1 + pad, (12 if pitched else 10)
+    poison = float("nan")
+    p2f = torch.full((B, ld_p2), poison, device=dev)
+    p2f[:, :K3] = f(p2)
+    o_a3, o_h1 = torch.full((B, ld_a3), -5.0, device=dev), torch.full((B, ld_h1), -5.0, device=dev)
+    o_dl = torch.full((B, ld_dl), -7.0, device=dev)
+    o_probs, o_rows, o_loss = torch.empty(B, 10, device=dev), torch.empty(B, device=dev), torch.zeros(1, device=dev)
+    o_dz1, o_dz3 = torch.empty(B, F1, device=dev), torch.empty(B, C3, device=dev)
+    ticket = torch.zeros(1, dtype=torch.int32, device=dev)
+    lm = 0 if mode == "ref" else 1
+    for _ in range(2):   # twice: the ticket must re-arm itself
+        native.head_fused(p2f, ld_p2 if pitched else 0, f(w3), f(b3), f(w1), f(b1), f(w2), f(b2), t, lm, o_a3,
+                          ld_a3 if pitched else 0, o_h1, ld_h1 if pitched else 0, o_probs, o_rows, o_loss, o_dl,
+                          ld_dl if pitched else 0, o_dz1, o_dz3, None, ticket, B)
+    torch.cuda.synchronize()
+    assert torch.allclose(o_a3[:, :C3].double(), a3, atol=2e-5, rtol=1e-5)
+    assert torch.allclose(o_h1[:, :F1].double(), h1, atol=2e-5, rtol=1e-5)
+    if pitched:   # padding columns are never written
+        assert (o_a3[:, C3:] == -5.0).all() and (o_h1[:, F1:] == -5.0).all() and (o_dl[:, 10:] == -7.0).all()
+    assert torch.allclose(o_probs.double(), probs, atol=1e-5)
+    assert abs(float(o_loss) - float(loss.detach())) < 1e-5
+    assert torch.allclose(o_dl[:, :10].double(), logits.grad, atol=1e-7, rtol=1e-3)
+    assert torch.allclose(o_dz1.double(), z1.grad, atol=1e-7, rtol=1e-3)
+    assert torch.allclose(o_dz3.double(), z3.grad, atol=1e-7, rtol=1e-3)
+    acc = torch.zeros(2, dtype=torch.float64, device=dev)
+    native.head_fused(p2f, ld_p2 if pitched else 0, f(w3), f(b3), f(w1), f(b1), f(w2), f(b2), t, lm, o_a3,
+                      ld_a3 if pitched else 0, o_h1, ld_h1 if pitched else 0, o_probs, o_rows, o_loss, None, 0, None, None,
+                      acc, ticket, B)
+    ref_sum = loss_fn(probs if mode == "ref" else logits, t, mode, reduction="sum")
+    assert abs(float(acc[0]) - float(ref_sum.detach())) < 1e-3
+    assert int(acc[1]) == int(probs.argmax(1).eq(t).sum())
+
+
 def test_linear_bwd_group():
     native = _native()
     torch.manual_seed(4)
