@@ -109,6 +109,31 @@ class Trainer:
         self._steps_at_log = 0
         self._pumps = {}
         self._loss_ring = None
+        self._ev_log = None
+
+    def _device_mark(self):
+        """A CUDA event on the current stream (device time per step for the JSONL)."""
+        if self.ctx.device.type != "cuda":
+            return None
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record(torch.cuda.current_stream(self.ctx.device))
+        return ev
+
+    @staticmethod
+    def _step_us(ev_a, ev_b, n_steps: int):
+        if ev_a is None or ev_b is None or n_steps <= 0:
+            return None
+        ev_b.synchronize()
+        return ev_a.elapsed_time(ev_b) * 1e3 / n_steps
+
+    def _peer_wait_us(self):
+        """Exposed part of the gradient exchange in the most recent step: how long the last bucket kept the final
+        kernel's first CTA waiting for the peers (device-measured, csrc/ll_reduce.cu; None off the push protocol).
+        Reads a device word, i.e. waits for the queued steps: only called when a JSONL log asked for it."""
+        st = self.stepper
+        if not (getattr(st, "fused_final", False) and getattr(st, "world", 1) > 1):
+            return None
+        return float(int(st.step_counter[3].item()) & 0xffffffff) / 1e3
 
     def _rate(self, n_steps: int, batch: int):
         """images/s of this rank since the previous log point (host wall clock; the log points are the only host
@@ -161,18 +186,29 @@ class Trainer:
         if self._loss_ring is None or self._loss_ring.numel() < n_batches:
             self._loss_ring = torch.zeros(max(n_batches, 64), dtype=torch.float32).pin_memory()
         last = None
+        timed = self.ctx.is_main and self.log._jsonl is not None      # device step times only when somebody records them
+        marks = [self._device_mark()] if timed else []                 # marks[i] = end of chunk i-1 on the stream
+        chunk_n = []
         for c0 in range(0, n_full, self.log_interval):
             n = min(self.log_interval, n_full - c0)
             pump.run(order[c0 * B:], n, self._loss_ring[c0:])
             self.global_step += n
+            if timed:
+                marks.append(self._device_mark())
+                chunk_n.append(n)
             if self.ctx.is_main:
                 pump.wait_first()
                 self.check_peers()
                 last = float(self._loss_ring[c0])
                 self.log.print(train_line(epoch, c0, B, len(loader.dataset), n_batches, last))
                 first = self.global_step - n + 1
+                # device time per step of the PREVIOUS chunk (finished: this chunk's first step has); the current chunk is
+                # still in flight
+                ci = len(chunk_n) - 1
+                step_us = self._step_us(marks[ci - 1], marks[ci], chunk_n[ci - 1]) if (timed and ci >= 1) else None
                 self.log.event(kind="train", epoch=epoch, step=first, batch_idx=c0, loss=last,
-                               images_per_s=self._rate(first - self._steps_at_log, B))
+                               images_per_s=self._rate(first - self._steps_at_log, B), step_us=step_us,
+                               peer_wait_us=self._peer_wait_us() if timed else None)
                 self._steps_at_log = first
         if run_ragged:                                        # ragged last batch: Python path
             idx = order[n_full * B:]
@@ -200,8 +236,12 @@ class Trainer:
                 last = float(loss.item())  # the only host sync on the step path (train.py:55)
                 self.check_peers()
                 self.log.print(train_line(epoch, batch_idx, len(data), len(loader.dataset), n_batches, last))
+                ev = self._device_mark() if self.log._jsonl is not None else None
+                step_us = self._step_us(self._ev_log, ev, self.global_step - self._steps_at_log)
+                self._ev_log = ev
                 self.log.event(kind="train", epoch=epoch, step=self.global_step, batch_idx=batch_idx, loss=last,
-                               images_per_s=self._rate(self.global_step - self._steps_at_log, len(data)))
+                               images_per_s=self._rate(self.global_step - self._steps_at_log, len(data)),
+                               step_us=step_us, peer_wait_us=self._peer_wait_us() if ev is not None else None)
                 self._steps_at_log = self.global_step
             if self.dry_run:
                 break

@@ -184,7 +184,12 @@ __global__ void __launch_bounds__(LL_NT, 2) reduce_update_ll_kernel(LLArgs a) {
                 if (world > 1) {
                     ll_push4(a.comm, parity, gen, idx, g);
                     const float4 own = a.comm.wire ? round_bf16x4(g) : g;
+                    // observability: how long the step's LAST bucket (pushed just above by every rank) kept CTA 0 waiting
+                    // for the peers = the exposed part of the exchange, in ns, readable at step_counter[3]
+                    const bool probe = blockIdx.x == 0 && tid == 0;
+                    const unsigned long long t0 = probe ? globaltimer_ns() : 0ull;
                     bad = !ll_gather4(a.comm, parity, gen, idx, own, timeout_ns, g);
+                    if (probe) a.step_counter[3] = (uint32_t)min(globaltimer_ns() - t0, 0xffffffffull);
                 }
                 if (!bad) ru_update(cx, idx, scale4(g, inv));
             }

@@ -223,7 +223,8 @@ int b200dp_conv_bwd_noalloc(const void* x, int in_is_u8, float mean, float std, 
  * scheduler changes.
  * step_counter (device, uint32[4], zero-initialised): [0] generation (= optimizer steps done),
  * [1] ticket, [2] error word (1 = a peer did not answer within comm->timeout_ms; sticky: later launches
- * skip the exchange and the update but keep the bookkeeping going).  The LAST
+ * skip the exchange and the update but keep the bookkeeping going), [3] (push protocol) nanoseconds the step's last
+ * bucket kept CTA 0 waiting for the peers' lines — the exposed part of the exchange.  The LAST
  * bucket launch of a step (last_bucket != 0) advances the generation.
  * loss_src / loss_sink (both nullable; used by the last bucket launch only): loss_sink is a device
  * uint64[3] = {address of a mapped pinned float array (0 = off), generation stored at index 0,
