@@ -41,6 +41,13 @@ from .parallel.launch import RankContext
 from .utils.logging import RankLogger, test_line, train_line
 
 
+def _nvtx(name: str, push: bool) -> None:
+    """NVTX range around a host-side phase (only once the native library is loaded: the CPU path has no use for it)."""
+    from .ops import native
+    if native.is_loaded():
+        native.nvtx_push(name) if push else native.nvtx_pop()
+
+
 class EagerStepper:
     """torch-eager forward/backward under :class:`DataParallel`."""
 
@@ -224,6 +231,13 @@ class Trainer:
         return last
 
     def train_epoch(self, loader, epoch: int) -> Optional[float]:
+        _nvtx("b200dp.train_epoch", True)
+        try:
+            return self._train_epoch(loader, epoch)
+        finally:
+            _nvtx("b200dp.train_epoch", False)
+
+    def _train_epoch(self, loader, epoch: int) -> Optional[float]:
         pump = self._pump_for(loader)
         if pump is not None:
             return self._train_epoch_pumped(pump, loader, epoch)
@@ -249,9 +263,11 @@ class Trainer:
         return last
 
     def test_epoch(self, loader) -> Tuple[float, int, int]:
+        _nvtx("b200dp.test_epoch", True)
         for data, target in loader:
             self.stepper.eval_batch(data, target)
         loss_sum, correct = self.stepper.eval_result()
+        _nvtx("b200dp.test_epoch", False)
         n = len(loader.dataset)
         if self.global_eval and self.ctx.world_size > 1:
             t = torch.tensor([loss_sum, correct, n], dtype=torch.float64, device=self.ctx.device)

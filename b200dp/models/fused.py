@@ -404,7 +404,9 @@ class NativeStepper:
 
     def _step_body(self, x: torch.Tensor, y: torch.Tensor) -> None:
         main = torch.cuda.current_stream(self.device)
+        native.nvtx_push("b200dp.forward")
         self.net.forward(x, y, train=True)
+        native.nvtx_pop()
         side = self.side
 
         bk = self.arena.layout.buckets
@@ -437,9 +439,11 @@ class NativeStepper:
             with torch.cuda.stream(side):
                 self._reduce_update(i)
 
+        native.nvtx_push("b200dp.backward+exchange+update")
         self.net.backward(x, on_bucket)
         if side is not None:
             main.wait_stream(side)
+        native.nvtx_pop()
 
     def train_step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         self._sync_hyper()
@@ -499,7 +503,9 @@ class NativeStepper:
 
     # ---- eval ----------------------------------------------------------------------
     def eval_batch(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        native.nvtx_push("b200dp.eval_forward")
         self.net.forward(x, y, train=False)
+        native.nvtx_pop()
 
     def eval_result(self, reset: bool = True) -> Tuple[float, int]:
         vals = self.net.eval_acc.tolist()        # the one D2H of the epoch

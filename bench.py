@@ -115,9 +115,9 @@ def _dtype_label(stepper):
     if stepper.dtype != "fp32":
         parts.append("tf32 tcgen05 GEMMs")
     if not parts:
-        return "fp32"
+        return "fp32 CUDA cores everywhere"
     rest = "fp32 CUDA cores elsewhere" if not (net.conv1_tc and stepper.dtype != "fp32") else "fp32 head"
-    return "bf16: " + " + ".join(parts) + "; " + rest + "; fp32 accumulation, storage and master weights"
+    return " + ".join(parts) + "; " + rest + "; fp32 accumulation, storage and master weights"
 
 
 def run_own(args):
@@ -222,7 +222,8 @@ def run_own(args):
             "ms_per_step": ms / K, "higher_is_better": True,
             "scaling": "strong" if args.config == "strong4096" else "weak",
             "vs_baseline": None,
-            "dtype": _dtype_label(stepper),
+            "dtype": "bf16" if (stepper.net.conv_tc or stepper.dtype != "fp32") else "fp32",
+            "dtype_detail": _dtype_label(stepper),
             "data": "synthetic", "impl": "b200dp",
             "config": {"model": "cnn.py LeNet" if args.config != "wide_cifar" else "cnn.py LeNet 4x wide, CIFAR-shaped",
                        "global_batch": batch * world, "per_gpu_batch": batch, "seq_len": None,

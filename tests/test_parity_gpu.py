@@ -118,3 +118,34 @@ def test_generic_dataparallel_world1_matches_torch_optim(opt, lr, bucket_bytes):
     for p, q in zip(model.parameters(), ref.parameters()):
         assert torch.allclose(p, q, atol=2e-6, rtol=1e-5), float((p - q).abs().max())
     assert list(model.state_dict().keys()) == list(ref.state_dict().keys())
+
+
+@pytest.mark.parametrize("dtype,conv,tol", [("auto", "auto", 2e-2), ("bf16", "auto", 2e-2), ("tf32", "simt", 5e-3)])
+def test_reduced_precision_paths_track_fp32_over_200_steps(dtype, conv, tol):
+    """The default kernel mix (bf16 tcgen05 convolutions, tf32 tcgen05 backward GEMMs) against the exact fp32 CUDA-core
+    path from the same initial weights on the same data: the loss trajectories must stay together over 200 Adadelta
+    steps (cross-entropy loss, learnable synthetic classes), and both must learn."""
+    from b200dp.data.synthetic import MNIST_SPEC, SyntheticImages
+    from b200dp.models.fused import NativeStepper
+    from b200dp.models.lenet import MNIST_LENET, LeNet
+    from b200dp.optim.flat import OptHyper
+    from b200dp.parallel.launch import RankContext
+    dev = torch.device("cuda", 0)
+    batch, steps = 128, 200
+    data = SyntheticImages(batch * 20, MNIST_SPEC, seed=9)
+    xs = [data.images[i * batch:(i + 1) * batch].to(dev) for i in range(20)]
+    ys = [data.targets[i * batch:(i + 1) * batch].to(dev) for i in range(20)]
+    curves = {}
+    for name, kw in (("fp32", dict(dtype="fp32", conv="simt")), ("test", dict(dtype=dtype, conv=conv))):
+        torch.manual_seed(5)
+        st = NativeStepper(RankContext(0, 1, 0, dev, "nccl"), MNIST_LENET, OptHyper("adadelta", lr=0.1), batch=batch,
+                           loss_mode="xent", graph=True, module=LeNet(MNIST_LENET), **kw)
+        curves[name] = [float(st.train_step(xs[i % 20], ys[i % 20])) for i in range(steps)]
+        if name == "test" and (dtype != "tf32"):
+            assert st.net.conv2_tc and st.net.convbwd_tc and not st.net.conv1_tc      # the hybrid really ran
+        st.close()
+    a, b = torch.tensor(curves["fp32"]), torch.tensor(curves["test"])
+    assert float(a[-10:].mean()) < 0.5 * float(a[:10].mean())          # learning, not noise
+    assert float(b[-10:].mean()) < 0.5 * float(b[:10].mean())
+    drift = float((a - b).abs().max())
+    assert drift < tol * max(1.0, float(a.abs().max())), drift
