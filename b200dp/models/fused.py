@@ -1,29 +1,29 @@
 """Native LeNet runner: the whole training step as a short fixed sequence of
 hand-written sm_100a kernels over flat arenas, replayed from a CUDA graph.
 
-Step = 11 launches on the CUDA-core path, 14 on the tensor-core path (reference: ~50 ATen/cuDNN/cuBLAS kernels +
-10 NCCL all-reduces + 10 divides + the optimizer's elementwise kernels, train.py:45-51):
+Default step for the reference LeNet = 9 launches (+1 push with more than one GPU); reference: ~50 ATen/cuDNN/cuBLAS
+kernels + 10 NCCL all-reduces + 10 divides + the optimizer's elementwise kernels, train.py:45-51:
 
-    main stream                                      side stream (overlapped)        tensor-core path
-    -----------------------------------------------  ------------------------------  ------------------------------------
-    (weight pack)                                                                    tcw_pack_weights (bf16 panels)
-    conv1 fwd   (normalise+upsample+conv+act+pool)                                   tcw_conv1_fwd   [tcgen05, bf16]
-    conv2 fwd   (conv+act+pool)                                                      tcw_conv2_fwd   [tcgen05, bf16]
-    conv3 fwd   (GEMM+bias+act)                                                      tc_gemm (split-K) [tcgen05, tf32]
-    fc1   fwd   (GEMM+bias+act)                                                      tc_gemm           [tcgen05, tf32]
-    head tail   (fc2+softmax+loss+dlogits+dz1)
-    head bwd A  {dW fc2, dW fc1, dZ3}  ------------> reduce+update bucket 0 (FC.*)   tc_gemm group of 3
-    head bwd B  {dW conv3, dP2}        ------------> reduce+update bucket 1 (conv3)  tc_gemm group of 2
-    conv bwd    (pool/act bwd, dgrad, 2x wgrad) ---> reduce+update bucket 2 (conv)   tcw_conv2_dgrad, tcw_conv_wgrad x2
+    main stream                                                      other streams (overlapped)
+    ---------------------------------------------------------------  ------------------------------------------
+    conv1 fwd   (normalise+upsample+conv+act+pool)   CUDA cores      tcw_pack_weights (bf16 panels)
+    conv2 fwd   (conv+act+pool)                      tcgen05 bf16
+    head_fused  (conv3+FC.0+FC.2+softmax+loss+dlogits+dz1+dz3) fp32
+    tc_gemm     {dW FC.2, dW FC.0, dW conv3, dP2}    tcgen05 tf32    grad_push of the two dense buckets (world > 1)
+    conv2 dgrad (pool/act bwd fused)                 tcgen05 bf16    conv2 wgrad (tcgen05 bf16)
+    conv1 wgrad                                      tcgen05 bf16
+                                                                     reduce_update_ll: partial rows + push + wait +
+                                                                     rank-order sum + average + optimizer, whole arena
 
-Which path runs is a measured choice (``dtype="auto"``, ``conv="auto"``): the reference LeNet is a few MFLOP per
-layer and is faster on the fused fp32 CUDA-core kernels; the 4x-wide model runs on the tensor cores.  Every launch
-uses programmatic dependent launch, so the chain's scheduling gaps overlap (csrc/common.cuh).
+Which kernel runs a layer is a measured choice (``dtype="auto"``, ``conv="auto"``; profiles/lenet_tc_vs_simt.md): conv1
+(K = 25) is faster on CUDA cores, everything from conv2 on is faster on the tensor cores; ``dtype="fp32", conv="simt"``
+keeps every layer on the exact fp32 CUDA-core kernels; the 4x-wide model runs 14 launches, all GEMM-shaped work on
+tcgen05, with one fused handshake reduce+update per bucket.  Every launch of the main chain uses programmatic dependent
+launch, so the chain's scheduling gaps overlap (csrc/common.cuh).
 
-The reduce+update launch is the fused P2P all-reduce + average + optimizer
-kernel (csrc/reduce_update.cu); with world size 1 it degenerates to the
-optimizer update.  ``state_dict`` keys/shapes are the reference's because the
-parameters are views of an eager :class:`LeNet` re-pointed into the arena.
+The gradient exchange is the fused P2P kernel pair of csrc/ll_reduce.cu (push protocol) or csrc/reduce_update.cu
+(handshake per bucket); with world size 1 both degenerate to the optimizer update.  ``state_dict`` keys/shapes are the
+reference's because the parameters are views of an eager :class:`LeNet` re-pointed into the arena.
 """
 from __future__ import annotations
 
