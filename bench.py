@@ -144,14 +144,21 @@ def run_own(args):
     n_pool = L2_BYTES // (batch * img_bytes) + 8
     g = torch.Generator(device="cpu").manual_seed(1234 + rank)
     pool_x = torch.randint(0, 256, (n_pool, batch, spec.channels, spec.height, spec.width), dtype=torch.uint8,
-                           generator=g).to(dev)
-    pool_y = torch.randint(0, spec.classes, (n_pool, batch), generator=g).to(dev)
-    sx, sy = torch.empty_like(pool_x[0]), torch.empty_like(pool_y[0])
+                           generator=g)
+    pool_y = torch.randint(0, spec.classes, (n_pool, batch), generator=g)
+    # images and labels of a batch sit in ONE pool row, so a step's inputs arrive with a single device copy
+    x_bytes = batch * img_bytes
+    y_off = (x_bytes + 15) // 16 * 16
+    pool = torch.zeros(n_pool, y_off + 8 * batch, dtype=torch.uint8)
+    pool[:, :x_bytes] = pool_x.view(n_pool, -1)
+    pool[:, y_off:] = pool_y.contiguous().view(torch.uint8).view(n_pool, -1)
+    pool = pool.to(dev)
+    slot = torch.empty(y_off + 8 * batch, dtype=torch.uint8, device=dev)
+    sx = slot[:x_bytes].view(batch, spec.channels, spec.height, spec.width)
+    sy = slot[y_off:].view(torch.int64)
 
     def dev_step(i):
-        j = i % n_pool
-        sx.copy_(pool_x[j], non_blocking=True)
-        sy.copy_(pool_y[j], non_blocking=True)
+        slot.copy_(pool[i % n_pool], non_blocking=True)
         return stepper.train_step(sx, sy)
 
     # clocks are sampled from before the warm-up until after the timed region (the timed region alone
