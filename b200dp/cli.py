@@ -58,6 +58,13 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--allreduce-algo", choices=["auto", "push", "oneshot", "twoshot", "nvls"], default="auto",
                    help="push = per-bucket P2P pushes + one wait/sum/update launch per step (whole-model gradients up to "
                         "1 MB); oneshot/twoshot/nvls = one handshake launch per bucket; auto = by size")
+    p.add_argument("--wire", choices=["auto", "fp32", "bf16"], default="auto",
+                   help="gradient wire format of the push protocol (auto: bf16 only with --dtype bf16)")
+    p.add_argument("--conv", choices=["auto", "simt", "tc", "hybrid"], default="auto",
+                   help="convolution kernels: CUDA cores, tcgen05 window-tile kernels, or hybrid (first layer on CUDA cores, "
+                        "the rest on tcgen05); auto = measured-fastest for the model")
+    p.add_argument("--peer-timeout-ms", type=int, default=0,
+                   help="bound on every wait for a peer rank's gradients (0 = 20 s); a rank that does not deliver raises")
     p.add_argument("--no-overlap", action="store_true", help="reduce after backward, not during it")
     p.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
     p.add_argument("--no-pump", action="store_true",

@@ -24,7 +24,7 @@ class StepPump:
     base row ``order[k*batch + j]``.  Ragged batches do not go through the pump (the graphs are
     captured for the full batch): feed them to ``stepper.train_step``."""
 
-    def __init__(self, stepper, images: torch.Tensor, targets: torch.Tensor, batch: int, *, depth: int = 3):
+    def __init__(self, stepper, images: torch.Tensor, targets: torch.Tensor, batch: int, *, depth: int = 6):
         assert not images.is_cuda and images.is_contiguous() and images.dtype in (torch.uint8, torch.float32), \
             "the pump streams raw uint8 samples (the first kernel normalises on the device) or float32 samples that " \
             "are already transformed"
@@ -35,11 +35,18 @@ class StepPump:
         assert self.batch == stepper.net.B, "the pump runs the stepper's full batch"
         dev = stepper.device
         shape = (self.batch,) + tuple(images.shape[1:])
-        self.host_x = [torch.empty(shape, dtype=images.dtype).pin_memory() for _ in range(depth)]
-        self.host_y = [torch.empty(self.batch, dtype=torch.int64).pin_memory() for _ in range(depth)]
-        self.dev_x = [torch.empty(shape, dtype=images.dtype, device=dev) for _ in range(depth)]
-        self.dev_y = [torch.empty(self.batch, dtype=torch.int64, device=dev) for _ in range(depth)]
-        self.h2d_bytes_per_step = self.host_x[0].numel() * images.element_size() + 8 * self.batch
+        # a ring slot is ONE allocation, [images | pad to 16 B | labels], on the host (pinned) and on the device: a step's
+        # upload is a single copy node in its graph (two nodes cost ~2 us more per step)
+        x_bytes = self.batch * images[0].numel() * images.element_size()
+        y_off = (x_bytes + 15) // 16 * 16
+        slot_bytes = (y_off + 8 * self.batch + 15) // 16 * 16
+        self.host_slot = [torch.empty(slot_bytes, dtype=torch.uint8).pin_memory() for _ in range(depth)]
+        self.dev_slot = [torch.empty(slot_bytes, dtype=torch.uint8, device=dev) for _ in range(depth)]
+        view_x = lambda t: t[:x_bytes].view(images.dtype).view(shape)        # noqa: E731
+        view_y = lambda t: t[y_off:y_off + 8 * self.batch].view(torch.int64)   # noqa: E731
+        self.host_x, self.host_y = [view_x(t) for t in self.host_slot], [view_y(t) for t in self.host_slot]
+        self.dev_x, self.dev_y = [view_x(t) for t in self.dev_slot], [view_y(t) for t in self.dev_slot]
+        self.h2d_bytes_per_step = x_bytes + 8 * self.batch
         self._graphs = []
         self._handle: Optional[int] = None
         self._loss_keepalive = None
@@ -60,11 +67,19 @@ class StepPump:
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 main = torch.cuda.current_stream(st.device)
-                copy_stream.wait_stream(main)
-                with torch.cuda.stream(copy_stream):              # branch 1: upload the NEXT step's batch
-                    self.dev_x[nxt].copy_(self.host_x[nxt], non_blocking=True)
-                    self.dev_y[nxt].copy_(self.host_y[nxt], non_blocking=True)
-                st._step_body(self.dev_x[s], self.dev_y[s])       # branch 2: this step
+
+                def prefetch(nxt=nxt):
+                    # branch 1: upload the NEXT step's batch, by a small kernel that reads the pinned slot over PCIe (a
+                    # memcpy node here cost ~4 us per step); forked after the step's first kernel
+                    copy_stream.wait_stream(main)
+                    with torch.cuda.stream(copy_stream):
+                        native.fetch_slot(self.dev_slot[nxt], self.host_slot[nxt])   # images + labels, one small kernel
+
+                st.net.after_first_kernel = prefetch
+                try:
+                    st._step_body(self.dev_x[s], self.dev_y[s])   # branch 2: this step
+                finally:
+                    st.net.after_first_kernel = None
                 main.wait_stream(copy_stream)
             self._graphs.append(g)
         d = native.PumpDesc()

@@ -290,7 +290,8 @@ def build_stepper(ctx: RankContext, args, cfg: LeNetConfig, hyper: OptHyper, spe
                              algo=getattr(args, "allreduce_algo", "auto"),
                              graph=not getattr(args, "no_graph", False),
                              overlap=not getattr(args, "no_overlap", False),
-                             dtype=getattr(args, "dtype", "auto"))
+                             dtype=getattr(args, "dtype", "auto"), conv=getattr(args, "conv", "auto"),
+                             wire=getattr(args, "wire", "auto"), timeout_ms=getattr(args, "peer_timeout_ms", 0))
     # --eager: torch kernels for the model; the gradient path is still ours (--backend b200, default on GPU) unless
     # --backend nccl/gloo asks for torch.distributed
     comm = "b200" if (ctx.device.type == "cuda" and backend in (None, "b200")) else "torch"

@@ -132,6 +132,7 @@ class NativeLeNet:
         # layer, conv2's weight gradient beside conv2's data gradient
         self.pack_stream = torch.cuda.Stream(device=self.device) if self.conv_tc else None
         self.parallel_wgrad = True
+        self.after_first_kernel = None  # optional callable run right after the first launch of a forward (see StepPump)
 
     def dims(self, b: int) -> native.Dims:
         c = self.cfg
@@ -159,6 +160,8 @@ class NativeLeNet:
         else:
             native.conv1_fwd(x, w["ConvNet.1.weight"], w["ConvNet.1.bias"], self.p1, self.idx1 if train else None,
                              d, self.spec.mean, self.spec.std)
+        if self.after_first_kernel is not None:
+            self.after_first_kernel()
         if fork is not None:
             fork.wait_stream(self.pack_stream)
         if self.conv2_tc:
@@ -348,11 +351,13 @@ class NativeStepper:
         self._static_y: Optional[torch.Tensor] = None
         self._warm = 0
         self._comm_off = False        # measurement aid: see set_comm_enabled
+        self._loss_posted = False
         self._pumps = []
         hf = self.net.head_fused
         n = (3 if hf else 5) + (1 if self.net.conv_tc else 0) + (1 if hf else 2) + (3 if self.net.convbwd_tc else 1)
         pushes = 0 if self.world == 1 else (1 if hf else 2)
         n += (1 + pushes) if self.fused_final else 3                                       # reduce/update (+ pushes)
+        n += 1 if overlap else 0                                                            # post_loss beside the backward
         self.launches_per_step = n            # forward + GEMM backward + conv backward + gradient exchange/update
 
     # ---- optimizer scalars live on the device so graph replays see scheduler changes ----
@@ -378,7 +383,7 @@ class NativeStepper:
                              net.partial_stride if is_conv else 0, opt.hyper.code(), self.hyper_dev,
                              self.step_counter, bucket_index == 2,
                              self._comm_struct(b.numel * 4, self.overlap and bucket_index != 2),
-                             net.loss, self.loss_sink)
+                             net.loss, None if self._loss_posted else self.loss_sink)
 
     def _push(self, bucket_index: int) -> None:
         """Push protocol: send a finished bucket to every peer, wait for nobody."""
@@ -400,7 +405,8 @@ class NativeStepper:
         native.reduce_update_ll(self.arena.param, self.arena.grad, opt.state0, opt.state1, None, 0,
                                 self.arena.layout.total, net.partials, net.cur_partials, net.partial_stride,
                                 conv.start, conv.numel, not pushed, opt.hyper.code(), self.hyper_dev,
-                                self.step_counter, self._comm_struct(0, False), net.loss, self.loss_sink)
+                                self.step_counter, self._comm_struct(0, False), net.loss,
+                                None if self._loss_posted else self.loss_sink)
 
     def _step_body(self, x: torch.Tensor, y: torch.Tensor) -> None:
         main = torch.cuda.current_stream(self.device)
@@ -408,6 +414,12 @@ class NativeStepper:
         self.net.forward(x, y, train=True)
         native.nvtx_pop()
         side = self.side
+        # the loss goes to the host from a one-thread kernel beside the backward pass (see b200dp_post_loss)
+        self._loss_posted = side is not None
+        if side is not None:
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                native.post_loss(self.net.loss, self.step_counter, self.loss_sink)
 
         bk = self.arena.layout.buckets
         both = self.net.head_fused and bk[1].stop == bk[0].start     # the two dense buckets finish in one launch
@@ -482,7 +494,7 @@ class NativeStepper:
         self._graphs[("static",)].replay()
         return self.net.loss
 
-    def make_pump(self, images: torch.Tensor, targets: torch.Tensor, batch: int, depth: int = 3):
+    def make_pump(self, images: torch.Tensor, targets: torch.Tensor, batch: int, depth: int = 6):
         """A native step pump (csrc/pump.cu) over the host arrays ``images`` (uint8) / ``targets``: queues whole
         runs of steps — sample gather into a pinned ring, H2D copy, this stepper's step, loss read-back — from
         a C++ loop.  See :class:`b200dp.data.pump.StepPump`."""

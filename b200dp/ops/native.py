@@ -102,12 +102,14 @@ def load(build_if_missing: bool = True):
     lib.b200dp_reduce_update.argtypes = [vp, vp, vp, vp, vp, i, i, vp, i, i, i, vp, vp, i, C.POINTER(Comm), vp, vp, vp]
     lib.b200dp_grad_push.argtypes = [vp, i, i, vp, C.POINTER(Comm), vp]
     lib.b200dp_reduce_update_ll.argtypes = [vp, vp, vp, vp, vp, i, i, vp, i, i, i, i, i, i, vp, vp, C.POINTER(Comm), vp, vp, vp]
+    lib.b200dp_post_loss.argtypes = [vp, vp, vp, vp]
     lib.b200dp_symm_alloc.argtypes = [C.POINTER(vp), C.c_uint64]
     lib.b200dp_symm_free.argtypes = [vp]
     lib.b200dp_symm_zero.argtypes = [vp, C.c_uint64]
     lib.b200dp_symm_export.argtypes = [vp, C.c_char_p]
     lib.b200dp_symm_import.argtypes = [C.c_char_p, C.POINTER(vp)]
     lib.b200dp_symm_close.argtypes = [vp]
+    lib.b200dp_fetch_slot.argtypes = [vp, vp, C.c_int64, vp]
     lib.b200dp_pump_create.argtypes = [C.POINTER(vp), C.POINTER(PumpDesc)]
     lib.b200dp_pump_run.argtypes = [vp, vp, i, vp]
     lib.b200dp_pump_wait_first.argtypes = [vp]
@@ -312,6 +314,11 @@ def reduce_update_ll(param, grad, state0, state1, shadow, start: int, count: int
                                          _stream()), "reduce_update_ll")
 
 
+def post_loss(loss_src, step_counter, loss_sink) -> None:
+    """One-thread kernel: the step's loss into the host's mapped array (see include/b200dp.h)."""
+    check(load().b200dp_post_loss(_p(loss_src), _p(step_counter), _p(loss_sink), _stream()), "post_loss")
+
+
 # ---- symmetric memory ------------------------------------------------------------
 def symm_alloc(nbytes: int) -> int:
     ptr = C.c_void_p()
@@ -344,6 +351,13 @@ def symm_close(ptr: int) -> None:
 
 
 # ---- native step pump ------------------------------------------------------------
+def fetch_slot(dst: torch.Tensor, src_pinned: torch.Tensor) -> None:
+    """Upload a pinned host slot into a device slot with a small kernel (the prefetch branch of a step graph)."""
+    nbytes = src_pinned.numel() * src_pinned.element_size()
+    assert dst.is_cuda and src_pinned.is_pinned() and dst.numel() * dst.element_size() == nbytes
+    check(load().b200dp_fetch_slot(dst.data_ptr(), src_pinned.data_ptr(), nbytes, _stream()), "fetch_slot")
+
+
 def pump_create(desc: PumpDesc) -> int:
     h = C.c_void_p()
     check(load().b200dp_pump_create(C.byref(h), C.byref(desc)), "pump_create")

@@ -230,6 +230,22 @@ __global__ void __launch_bounds__(LL_NT, 2) reduce_update_ll_kernel(LLArgs a) {
 
 using namespace b200dp;
 
+// The step's loss goes to the host as a 4-byte store into a mapped pinned array (no copy command).  A kernel that has
+// stored to host memory stays alive until the store has crossed PCIe (~5 us), so the store gets a one-thread kernel of
+// its own on a stream beside the backward pass instead of riding in a kernel of the step's dependency chain.
+__global__ void post_loss_kernel(const float* loss_src, const uint32_t* step_counter, const unsigned long long* sink) {
+    const unsigned long long ring = sink[0], idx = (unsigned long long)(step_counter[0] + 1u) - sink[1];
+    if (ring != 0ull && idx < sink[2]) reinterpret_cast<volatile float*>(ring)[idx] = __ldcg(loss_src);
+}
+
+extern "C" int b200dp_post_loss(const float* loss_src, const uint32_t* step_counter, const uint64_t* loss_sink,
+                                b200dp_stream_t s) {
+    B200DP_REQUIRE(loss_src && step_counter && loss_sink, "null argument");
+    post_loss_kernel<<<1, 1, 0, (cudaStream_t)s>>>(loss_src, step_counter, (const unsigned long long*)loss_sink);
+    B200DP_CHECK(cudaGetLastError());
+    return 0;
+}
+
 static int ll_check_comm(const b200dp_comm* comm, int start, int count) {
     B200DP_REQUIRE(comm->world >= 2 && comm->world <= 8, "world size 2..8");
     B200DP_REQUIRE(comm->rank >= 0 && comm->rank < comm->world, "rank out of range");

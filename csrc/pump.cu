@@ -261,6 +261,28 @@ extern "C" int b200dp_pump_destroy(b200dp_pump* handle) {
     return 0;
 }
 
+// ---- host -> device upload by a kernel ---------------------------------------------------------------------------
+// The next step's batch is uploaded beside the running step.  As a memcpy NODE in the step's graph that upload cost
+// ~4 us per step on the critical path (the copy engine's set-up serialises with the graph's kernel launches); as a small
+// KERNEL node that reads the pinned slot through its mapped address it is just another parallel branch.  A few CTAs
+// are enough to keep PCIe busy and leave the SMs to the step.
+__global__ void __launch_bounds__(256) fetch_slot_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src, long n16) {
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (long)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
+extern "C" int b200dp_fetch_slot(void* dst_device, const void* src_pinned_host, int64_t bytes, b200dp_stream_t s) {
+    B200DP_REQUIRE(dst_device && src_pinned_host && bytes > 0 && bytes % 16 == 0, "16-byte multiple required");
+    B200DP_REQUIRE((((uintptr_t)dst_device | (uintptr_t)src_pinned_host) & 15) == 0, "16-byte alignment required");
+    void* dev_view = nullptr;    // the device-side address of the pinned host slot (identical under UVA, but ask)
+    B200DP_CHECK(cudaHostGetDevicePointer(&dev_view, const_cast<void*>(src_pinned_host), 0));
+    const long n16 = bytes / 16;
+    int grid = (int)((n16 + 255) / 256);
+    if (grid > 8) grid = 8;
+    fetch_slot_kernel<<<grid, 256, 0, (cudaStream_t)s>>>((uint4*)dst_device, (const uint4*)dev_view, n16);
+    B200DP_CHECK(cudaGetLastError());
+    return 0;
+}
+
 // ---- NVTX ranges for the Python side (profiling aid; no-ops without a tool attached) ----
 extern "C" void b200dp_nvtx_push(const char* name) { nvtxRangePushA(name); }
 extern "C" void b200dp_nvtx_pop(void) { nvtxRangePop(); }

@@ -286,6 +286,14 @@ int b200dp_reduce_update_ll(float* param, float* grad, float* state0, float* sta
                             uint32_t* step_counter, const b200dp_comm* comm, const float* loss_src,
                             const uint64_t* loss_sink, b200dp_stream_t s);
 
+/* The step's loss to the host without a copy command and off the step's dependency chain: a one-thread kernel stores
+ * *loss_src into the mapped pinned array described by loss_sink (slot = step_counter[0] + 1 - sink[1]; see
+ * b200dp_reduce_update).  Launch it on a stream beside the backward pass, after the kernel that produced the loss and
+ * before the step's last reduce+update launch (which advances step_counter[0]); pass that launch loss_sink = NULL.
+ * (A kernel that stores to host memory stays alive for a PCIe round trip; inside the last kernel of the step that was
+ * 5 us per step.)  Replaces train.py:55 loss.item(). */
+int b200dp_post_loss(const float* loss_src, const uint32_t* step_counter, const uint64_t* loss_sink, b200dp_stream_t s);
+
 /* ---- symmetric memory plumbing (replaces the NCCL communicator of train.py:26-31) ----
  * Allocation of peer-mappable device memory and exchange via CUDA IPC handles
  * (64 opaque bytes each, shipped between ranks by torch.distributed at start-up). */
@@ -322,6 +330,10 @@ typedef struct {
     void* dev_y[B200DP_PUMP_MAX_DEPTH];
     void* graph_exec[B200DP_PUMP_MAX_DEPTH];  /* cudaGraphExec_t per slot */
 } b200dp_pump_desc;
+/* Upload of one ring slot by a small kernel that reads the pinned host slot through its mapped address (bytes: multiple
+ * of 16, both pointers 16-byte aligned).  Meant as the prefetch branch of a step's graph: a kernel node there costs
+ * nothing on the step's critical path, a memcpy node cost ~4 us per step.  Replaces train.py:45 (.cuda() copies). */
+int b200dp_fetch_slot(void* dst_device, const void* src_pinned_host, int64_t bytes, b200dp_stream_t s);
 int b200dp_pump_create(b200dp_pump** out, const b200dp_pump_desc* desc);
 int b200dp_pump_run(b200dp_pump* p, const int64_t* order, int n_steps, b200dp_stream_t s);
 int b200dp_pump_wait_first(b200dp_pump* p);   /* until step 0 of the latest run finished */
