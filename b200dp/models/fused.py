@@ -352,6 +352,7 @@ class NativeStepper:
         self._warm = 0
         self._comm_off = False        # measurement aid: see set_comm_enabled
         self._loss_posted = False
+        self._eval_graphs, self._eval_warm = 0, False
         self._pumps = []
         hf = self.net.head_fused
         n = (3 if hf else 5) + (1 if self.net.conv_tc else 0) + (1 if hf else 2) + (3 if self.net.convbwd_tc else 1)
@@ -471,7 +472,7 @@ class NativeStepper:
         key = (x.data_ptr(), y.data_ptr(), b)
         gph = self._graphs.get(key)
         if gph is None:
-            if len(self._graphs) >= self.MAX_GRAPHS:
+            if len(self._graphs) - self._eval_graphs >= self.MAX_GRAPHS:
                 return self._replay_static(x, y)
             gph = self._capture(x, y)
             self._graphs[key] = gph
@@ -509,14 +510,37 @@ class NativeStepper:
         stays the same.  Replicas diverge while it is off — use only at the end of a benchmark."""
         self._comm_off = not on
         self._graphs.clear()
+        self._eval_graphs = 0
         for p in self._pumps:
             p.invalidate()
         self._static_x = self._static_y = None
 
     # ---- eval ----------------------------------------------------------------------
     def eval_batch(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        """Forward + device-side metric accumulation (train.py:60-72 without the two host syncs per batch).  Full
+        batches replay a CUDA graph per input buffer (the loader's device ring has three), like the training step."""
         native.nvtx_push("b200dp.eval_forward")
-        self.net.forward(x, y, train=False)
+        key = ("eval", x.data_ptr(), y.data_ptr(), x.shape[0])
+        if not (self.use_graph and x.shape[0] == self.net.B and self._warm >= 2):
+            self.net.forward(x, y, train=False)
+        else:
+            gph = self._graphs.get(key)
+            if gph is None and self._eval_graphs < self.MAX_GRAPHS:
+                if not self._eval_warm:
+                    self.net.forward(x, y, train=False)          # lazy set-up outside capture, once
+                    self._eval_warm = True
+                    native.nvtx_pop()
+                    return
+                torch.cuda.synchronize(self.device)
+                gph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gph, capture_error_mode="thread_local"):
+                    self.net.forward(x, y, train=False)
+                self._graphs[key] = gph
+                self._eval_graphs += 1
+            if gph is None:
+                self.net.forward(x, y, train=False)
+            else:
+                gph.replay()
         native.nvtx_pop()
 
     def eval_result(self, reset: bool = True) -> Tuple[float, int]:

@@ -4,8 +4,10 @@ reference's NCCL path (dist.all_reduce + '/= size' + optimizer.step), device-tim
 
     python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 bench/allreduce_sweep.py
 
-Roofline: bytes that must cross NVLink per rank / measured peer bandwidth (770 GB/s per direction):
-one-shot pulls (N-1) x bytes in; two-shot / NVLS pull (N-1)/N x bytes in and push the same out.
+Roofline: bytes that must cross NVLink per rank / peer bandwidth (770 GB/s per direction: the peer-copy rate measured
+on this pool's B200s, /opt/skills/guides/B200_PROFILING.md; nominal 900): one-shot pulls (N-1) x bytes in; two-shot /
+NVLS pull (N-1)/N x bytes in and push the same out; the push protocol (<= 1 MB) sends 2 (N-1) x bytes out (every 4
+payload bytes travel with a 4-byte flag).
 """
 import json
 import os
@@ -49,6 +51,8 @@ def main():
     n_max = max_bytes // 4
     native.load()
     comm = P2PComm(n_max, rank, world, algo=os.environ.get("SWEEP_TRANSPORT_ALGO", "nvls"))
+    push_max = min(max_bytes, 1 << 20)                      # the push protocol's regime
+    comm_ll = P2PComm(push_max // 4, rank, world, algo="push")
     param = torch.zeros(n_max, device=dev)
     grad = torch.randn(n_max, device=dev) * 1e-3
     s0, s1 = torch.zeros(n_max, device=dev), torch.zeros(1, device=dev)
@@ -84,6 +88,13 @@ def main():
             rec[f"{algo}_us"] = timed(fused_step, iters)
             wire = (world - 1) * n * 4 if algo == "oneshot" else (world - 1) / world * n * 4
             rec[f"{algo}_roofline_frac"] = (wire / (LINK_GBS * 1e9)) / (rec[f"{algo}_us"] * 1e-6)
+        if size <= push_max:
+            st_ll = comm_ll.struct_for(0)
+
+            def push_step():   # one launch: push + wait + rank-order sum + average + momentum update
+                native.reduce_update_ll(param, grad, s0, s1, None, 0, n, None, 0, 0, 0, 0, True, OPT_SGD, hyper, counter, st_ll)
+            rec["push_us"] = timed(push_step, iters)
+            rec["push_roofline_frac"] = (2 * (world - 1) * n * 4 / (LINK_GBS * 1e9)) / (rec["push_us"] * 1e-6)
         if int(counter[2]) != 0:
             raise RuntimeError("peer timeout flag set")
         rows.append(rec)
@@ -95,6 +106,7 @@ def main():
         out = os.environ.get("SWEEP_OUT", "gpurun_out/allreduce_sweep_n%d.json" % world)
         os.makedirs(os.path.dirname(out), exist_ok=True)
         json.dump({"transport": comm.transport, "multicast": bool(comm.multicast_ptr), "rows": rows}, open(out, "w"), indent=1)
+    comm_ll.close()
     comm.close()
     dist.destroy_process_group()
 
