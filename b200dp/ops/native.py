@@ -80,6 +80,8 @@ def load(build_if_missing: bool = True):
     lib.b200dp_head_fused_supported.argtypes = [i, i, i, i]
     lib.b200dp_head_fused_set_debug.argtypes = [vp]
     lib.b200dp_head_fused_set_debug.restype = None
+    lib.b200dp_head_fused_set_tma.argtypes = [i]
+    lib.b200dp_head_fused_set_tma.restype = None
     lib.b200dp_head_fused.argtypes = [vp, i, vp, vp, vp, vp, vp, vp, vp, i, vp, i, vp, i, vp, vp, vp, vp, i, vp, vp, vp, vp,
                                       i, i, i, i, i, vp]
     lib.b200dp_linear_bwd_group.argtypes = [C.POINTER(BwdProblem), i, vp]

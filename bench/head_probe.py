@@ -35,7 +35,8 @@ for _ in range(5):
     run()
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-for train in (True, False):
+for tma, train in ((1, True), (1, False), (0, True)):
+    native.load().b200dp_head_fused_set_tma(tma)
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g):
         for _ in range(20):
@@ -47,7 +48,8 @@ for train in (True, False):
         g.replay()
     e1.record()
     torch.cuda.synchronize()
-    print(f"head_fused train={train} B={B}: {e0.elapsed_time(e1) * 10:.2f} us per launch (graph, back to back)")
+    print(f"head_fused tma={tma} train={train} B={B}: {e0.elapsed_time(e1) * 10:.2f} us per launch (graph, back to back)")
+native.load().b200dp_head_fused_set_tma(1)
 
 # phase stamps of CTA 0 (cycles since its start), one isolated launch after warm-up
 dbg = torch.zeros(16, dtype=torch.int64, device=dev)

@@ -12,11 +12,14 @@
 //
 // Work split inside a CTA (512 threads, 4 batch rows): a dense layer out[r][n] = sum_k in[r][k] W(k,n) is computed with
 // thread = (two output columns, one of 8 k-groups) holding 2 x 4 row accumulators; the weights stream through shared memory in
-// 64-deep k-slabs (a cp.async ring running three slabs ahead, see "weight stream"), inputs sit transposed [k][4 rows] so
+// 64-deep k-slabs (a 4-stage ring running three slabs ahead, filled by TMA tensor-map copies — or by cp.async for shapes
+// TMA cannot address —, see "weight stream"), inputs sit transposed [k][4 rows] so
 // one 128-bit broadcast read serves 4 FMAs.  The k-quarters are added in fixed order: bit-reproducible.  (8 rows x 256
 // threads, the first layout, left 2 warps per scheduler to hide every shared-memory latency: 25 us.)
-// FC.2 / softmax / loss / dlogits / dz1 use one warp per row (84 x 10: too small for the slab machinery).
+// FC.2 / softmax / loss / dlogits / dz1 are spread over the 16 warps in three short stages (84 x 10: too small for the
+// slab machinery).
 #include "common.cuh"
+#include "tc_common.cuh"
 
 namespace b200dp {
 
@@ -32,6 +35,7 @@ constexpr int HF_MAXC = 16;      // classes
 constexpr int HF_SLAB_REGS = HF_BK * HF_NMAX / HF_NT;   // weights per thread per slab
 constexpr int HF_KPT = HF_BK / HF_KG;                    // k per thread per slab
 static_assert(HF_R == 4, "one 128-bit read per k serves the 4 row accumulators");
+static_assert(HF_KPT == 8, "a thread's k range of a slab is two 16-byte chunks");
 constexpr int HF_STAGES = 4;     // weight-slab ring depth
 
 struct HeadFusedArgs {
@@ -44,12 +48,16 @@ struct HeadFusedArgs {
     double* eval_acc; int* ticket;
     int B, K3, C3, F1, NC, loss_mode;
     long long* dbg;          // profiling aid: CTA 0 stores clock64() stamps of its phases here (NULL = off)
+    // TMA variant: tensor maps over W3 [C3][K3] (box 32 k x 128 n), W1 [F1][C3] as k-major operand (box 32 k x 128 n)
+    // and as n-major operand (box 32 n x 64 m); SWIZZLE_128B, out-of-bounds elements arrive as zeros
+    CUtensorMap tm3, tm1k, tm1n;
 };
 
 // ---- weight stream ------------------------------------------------------------------------------------------
-// All dense layers of the kernel consume ONE static sequence of 32-deep weight slabs (conv3's, then FC.0's, then FC.0
-// transposed for dz3).  The slabs travel global -> shared with cp.async (no registers, no thread waits for its own
-// loads) through a ring of HF_STAGES buffers that runs HF_STAGES-1 slabs ahead of the math and across layer
+// All dense layers of the kernel consume ONE static sequence of 64-deep weight slabs (conv3's, then FC.0's, then FC.0
+// transposed for dz3).  The slabs travel global -> shared by TMA (cp.async.bulk.tensor.2d through SWIZZLE_128B tensor maps,
+// one elected thread, completion on an mbarrier per stage: 12.7 us per launch) or, for weight shapes whose rows are not
+// 16-byte multiples, by cp.async (15.5 us) through a ring of HF_STAGES buffers that runs HF_STAGES-1 slabs ahead of the math and across layer
 // boundaries: a CTA has to stream all 232 KB of weights through one SM, so what matters is that several slabs are
 // always in flight (first generation: register prefetch one slab ahead = one L2 latency per slab, 23.6 us).
 // Wt(k, n) = W[n * sn + k * sk]; exactly one of sn / sk is 1.
@@ -62,6 +70,8 @@ struct HfLayer { const float* W; int sn, sk, N, K, nslab; };
 constexpr int HF_PK = HF_BK + 4;            // k-major slab pitch (floats)
 constexpr int HF_PN = HF_NMAX + 4;          // n-major slab pitch
 constexpr int HF_STAGE = HF_NMAX * HF_PK;   // floats per ring stage (>= HF_BK * HF_PN)
+constexpr uint32_t HF_TMA_SLAB_BYTES = HF_BK * HF_NMAX * 4;   // a TMA slab is dense: 64 x 128 floats
+static_assert(HF_STAGE * 4 % 1024 == 0 && HF_STAGE * 4 >= (int)HF_TMA_SLAB_BYTES, "SWIZZLE_128B stages: 1024-byte aligned");
 static_assert(HF_STAGE >= HF_BK * HF_PN, "stage must hold either orientation");
 
 __device__ __forceinline__ void hf_cp(float* dst, const float* src, int bytes, bool valid) {
@@ -136,6 +146,29 @@ struct HfStream {
         if (l == 2) L = layer[2];
         return L;
     }
+    // TMA variant: ONE thread issues a slab as 2 (k-major: two 32-k boxes of 128 rows) or 4 (n-major: four 32-n boxes of
+    // 64 rows) tensor copies of 8-16 KB that complete on the stage's mbarrier — no load/store-unit work at all, where the
+    // cp.async ring spends 64 warp-wide LDGSTS per slab.
+    __device__ __forceinline__ void issue_next_tma(int tid, const HeadFusedArgs& a, uint32_t bars) {
+        if (tid == 0 && issued < total) {
+            int g = issued, l = 0;
+            if (g >= layer[0].nslab) { g -= layer[0].nslab; l = 1; }
+            if (l == 1 && g >= layer[1].nslab) { g -= layer[1].nslab; l = 2; }
+            const int st = issued % HF_STAGES;
+            const uint32_t dst = smem_u32(ring + st * HF_STAGE), bar = bars + 8u * st;
+            fence_proxy_async_smem();                    // the stage was last read through the generic proxy
+            mbar_expect_tx(bar, HF_TMA_SLAB_BYTES);
+            if (l == 2) {
+#pragma unroll
+                for (int b = 0; b < 4; ++b) tma_load_2d(dst + b * (HF_BK * 128), &a.tm1n, bar, 32 * b, g * HF_BK);
+            } else {
+                const CUtensorMap* tm = (l == 0) ? &a.tm3 : &a.tm1k;
+#pragma unroll
+                for (int b = 0; b < 2; ++b) tma_load_2d(dst + b * (HF_NMAX * 128), tm, bar, g * HF_BK + 32 * b, 0);
+            }
+        }
+        ++issued;
+    }
     __device__ __forceinline__ void issue_next(int tid) {
         if (issued < total) {
             int g = issued, l = 0;
@@ -152,17 +185,50 @@ struct HfStream {
 // layer whose slabs are global slabs [g0, g0 + nslab).  sIn: [ceil64(K)][HF_R] floats, rows k >= K zero.  One 128-bit
 // broadcast read of the inputs serves both columns: 12 shared-memory reads per 64 FMAs.  The barrier at the top of
 // every slab also publishes whatever the caller wrote to shared memory before the call.
+template <bool TMA>
 __device__ __forceinline__ void hf_gemm(HfStream& st, int g0, int nslab, bool kmajor, const float* sIn,
-                                        float (&acc)[2][HF_R], int tid) {
+                                        float (&acc)[2][HF_R], int tid, const HeadFusedArgs& a, uint32_t bars) {
     const int cn = tid & (HF_CT - 1), kg = tid / HF_CT;
     for (int t = 0; t < nslab; ++t) {
-        hf_wait<HF_STAGES - 2>();      // this thread's copies of slab g0+t have landed ...
-        __syncthreads();               // ... everyone's have, and everyone is done reading slab g0+t-1
-        st.issue_next(tid);            // refill the buffer slab g0+t-1 occupied
+        if constexpr (TMA) {
+            mbar_wait(bars + 8u * ((g0 + t) % HF_STAGES), ((g0 + t) / HF_STAGES) & 1);   // slab g0+t has landed
+            __syncthreads();           // everyone is done reading slab g0+t-1
+            st.issue_next_tma(tid, a, bars);
+        } else {
+            hf_wait<HF_STAGES - 2>();  // this thread's copies of slab g0+t have landed ...
+            __syncthreads();           // ... everyone's have, and everyone is done reading slab g0+t-1
+            st.issue_next(tid);        // refill the buffer slab g0+t-1 occupied
+        }
         const float* in = sIn + (t * HF_BK + kg * HF_KPT) * HF_R;
         const float* stage = st.ring + ((g0 + t) % HF_STAGES) * HF_STAGE;
         float wv[2][HF_KPT];
-        if (kmajor) {
+        if constexpr (TMA) {
+            // SWIZZLE_128B box: logical (row r, 16-byte chunk q) sits at r * 128 + ((q ^ (r & 7)) << 4)
+            const char* sb = reinterpret_cast<const char*>(stage);
+            if (kmajor) {      // boxes = k halves, rows = output columns; this thread's 8 k are chunks 2 kq, 2 kq + 1 of its box
+                const int box = kg / 4, kq = kg & 3;
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    const int n = cn + c * HF_CT;
+                    const char* rowp = sb + box * (HF_NMAX * 128) + n * 128;
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        const float4 w4 = *reinterpret_cast<const float4*>(rowp + (((2 * kq + q) ^ (n & 7)) << 4));
+                        wv[c][q * 4] = w4.x; wv[c][q * 4 + 1] = w4.y; wv[c][q * 4 + 2] = w4.z; wv[c][q * 4 + 3] = w4.w;
+                    }
+                }
+            } else {           // boxes = 32-column groups, rows = k; row index & 7 == kk because kg * 8 is a multiple of 8
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    const int n = cn + c * HF_CT;
+                    const char* colp = sb + (n >> 5) * (HF_BK * 128) + (n & 3) * 4;
+                    const int q = (n & 31) >> 2;
+#pragma unroll
+                    for (int kk = 0; kk < HF_KPT; ++kk)
+                        wv[c][kk] = *reinterpret_cast<const float*>(colp + (kg * HF_KPT + kk) * 128 + ((q ^ kk) << 4));
+                }
+            }
+        } else if (kmajor) {
 #pragma unroll
             for (int c = 0; c < 2; ++c)
 #pragma unroll
@@ -207,8 +273,11 @@ __device__ __forceinline__ float hf_combine(float* sRed, const float (&acc)[2][H
 }
 static_assert(HF_NT == HF_R * HF_NMAX, "one output element per thread in the layer epilogues");
 
-__global__ void __launch_bounds__(HF_NT, 1) head_fused_kernel(HeadFusedArgs a) {
-    extern __shared__ __align__(16) float smem[];
+template <bool TMA>
+__global__ void __launch_bounds__(HF_NT, 1) head_fused_kernel(const __grid_constant__ HeadFusedArgs a) {
+    extern __shared__ __align__(1024) float smem[];     // SWIZZLE_128B ring stages need 1024-byte alignment
+    __shared__ __align__(8) unsigned long long sBar[HF_STAGES];
+    const uint32_t bars = smem_u32(sBar);
     const int K3P = (a.K3 + HF_BK - 1) / HF_BK * HF_BK;
     float* sX = smem;                                   // [K3P][8]   conv3 input rows, transposed
     float* sW = sX + K3P * HF_R;                        // [HF_STAGES][HF_STAGE]  weight-slab ring
@@ -240,10 +309,22 @@ __global__ void __launch_bounds__(HF_NT, 1) head_fused_kernel(HeadFusedArgs a) {
     st.total = st.layer[0].nslab + st.layer[1].nslab + (train ? st.layer[2].nslab : 0);
     st.issued = 0;
     st.ring = sW;
-    for (int i = tid; i < a.NC * a.F1; i += HF_NT) hf_cp(sW2 + i, a.w2 + i, 4, true);      // joins the first group
-    if (tid < a.NC) hf_cp(sW2 + a.NC * a.F1 + tid, a.b2 + tid, 4, true);
+    if constexpr (TMA) {
+        if (tid == 0) {
+            for (int i = 0; i < HF_STAGES; ++i) mbar_init(bars + 8u * i, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
 #pragma unroll 1
-    for (int i = 0; i < HF_STAGES - 1; ++i) st.issue_next(tid);
+        for (int i = 0; i < HF_STAGES - 1; ++i) st.issue_next_tma(tid, a, bars);
+        for (int i = tid; i < a.NC * a.F1; i += HF_NT) sW2[i] = __ldg(a.w2 + i);
+        if (tid < a.NC) sW2[a.NC * a.F1 + tid] = __ldg(a.b2 + tid);
+    } else {
+        for (int i = tid; i < a.NC * a.F1; i += HF_NT) hf_cp(sW2 + i, a.w2 + i, 4, true);      // joins the first group
+        if (tid < a.NC) hf_cp(sW2 + a.NC * a.F1 + tid, a.b2 + tid, 4, true);
+#pragma unroll 1
+        for (int i = 0; i < HF_STAGES - 1; ++i) st.issue_next(tid);
+    }
     for (int i = tid; i < HF_NMAX * HF_R; i += HF_NT) { sA3[i] = 0.f; sH1[i] = 0.f; sDz1[i] = 0.f; }
     mark();   // 1: ring primed, FC.2 weights staged
     pdl_wait();
@@ -270,7 +351,7 @@ __global__ void __launch_bounds__(HF_NT, 1) head_fused_kernel(HeadFusedArgs a) {
         for (int c = 0; c < 2; ++c)
 #pragma unroll
             for (int r = 0; r < HF_R; ++r) acc[c][r] = 0.f;
-        hf_gemm(st, g0, nslab, l != 2, sIn, acc, tid);  // its first barrier publishes the previous layer's outputs
+        hf_gemm<TMA>(st, g0, nslab, l != 2, sIn, acc, tid, a, bars);  // its first barrier publishes the previous layer's outputs
         g0 += nslab;
         mark();   // 4 / 6 / 9: slabs of layer l consumed
         const float pre = hf_combine(sRed, acc, tid);
@@ -406,7 +487,35 @@ __global__ void __launch_bounds__(HF_NT, 1) head_fused_kernel(HeadFusedArgs a) {
 
 using namespace b200dp;
 
+typedef CUresult (*HfEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static HfEncodeFn hf_encoder() {
+    static HfEncodeFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) == cudaSuccess &&
+            qr == cudaDriverEntryPointSuccess)
+            fn = (HfEncodeFn)p;
+    }
+    return fn;
+}
+// [rows][cols] fp32, dense rows; box = {32 floats (128 bytes: the SWIZZLE_128B span), box_rows}; zeros out of bounds
+static bool hf_encode(CUtensorMap* tm, const float* ptr, int rows, int cols, int box_rows) {
+    HfEncodeFn enc = hf_encoder();
+    if (enc == nullptr || ((uintptr_t)ptr & 15) != 0 || cols % 4 != 0) return false;
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)cols * 4};
+    cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 static long long* g_hf_dbg = nullptr;
+static int g_hf_tma = 1;
+extern "C" void b200dp_head_fused_set_tma(int on) { g_hf_tma = on; }
 extern "C" void b200dp_head_fused_set_debug(long long* dbg) { g_hf_dbg = dbg; }
 
 extern "C" int b200dp_head_fused_supported(int K3, int C3, int F1, int ncls) {
@@ -430,10 +539,23 @@ extern "C" int b200dp_head_fused(const float* p2, int ld_p2, const float* w3, co
                     dz3, eval_acc, ticket, B, K3, C3, F1, ncls, loss_mode, g_hf_dbg};
     const int K3P = (K3 + HF_BK - 1) / HF_BK * HF_BK;
     const size_t smem = (size_t)(K3P * HF_R + HF_STAGES * HF_STAGE + HF_KG * HF_R * HF_NMAX + 3 * HF_NMAX * HF_R + ncls * F1 + ncls) * sizeof(float);
-    static DeviceOnce attr;
-    if (smem > 48 * 1024) B200DP_CHECK(attr.max_dynamic_smem(head_fused_kernel, (int)smem));
     const int grid = (B + HF_R - 1) / HF_R;
-    B200DP_CHECK(launch_pdl(head_fused_kernel, dim3(grid), dim3(HF_NT), smem, (cudaStream_t)s, a));
+    // weights by TMA tensor map when the rows are 16-byte multiples (the reference geometry: 400 and 120 floats); the
+    // cp.async ring serves every other shape
+    const bool tma = g_hf_tma && hf_encode(&a.tm3, w3, C3, K3, HF_NMAX) && hf_encode(&a.tm1k, w1, F1, C3, HF_NMAX) &&
+                     hf_encode(&a.tm1n, w1, F1, C3, HF_BK);
+    // the attribute is set once per device, so to the kernel's ceiling, not to this call's need (K3 varies between calls)
+    constexpr int kSmemCeiling = 224 * 1024;    // 227 KB per CTA minus room for the static part
+    B200DP_REQUIRE(smem <= (size_t)kSmemCeiling, "K3 too large for the fused head's shared-memory budget");
+    if (tma) {
+        static DeviceOnce attr;
+        B200DP_CHECK(attr.max_dynamic_smem(head_fused_kernel<true>, kSmemCeiling));
+        B200DP_CHECK(launch_pdl(head_fused_kernel<true>, dim3(grid), dim3(HF_NT), smem, (cudaStream_t)s, a));
+    } else {
+        static DeviceOnce attr;
+        B200DP_CHECK(attr.max_dynamic_smem(head_fused_kernel<false>, kSmemCeiling));
+        B200DP_CHECK(launch_pdl(head_fused_kernel<false>, dim3(grid), dim3(HF_NT), smem, (cudaStream_t)s, a));
+    }
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }

@@ -82,6 +82,9 @@ int b200dp_head_tail(const float* h1, const float* w, const float* b, const int6
 int b200dp_head_fused_supported(int K3, int C3, int F1, int ncls);
 /* Profiling aid: while dbg != NULL, CTA 0 of every fused-head launch stores clock64() stamps of its phases in dbg[0..16). */
 void b200dp_head_fused_set_debug(long long* dbg);
+/* The weights reach shared memory by TMA tensor maps (cp.async.bulk.tensor, SWIZZLE_128B; default, needs 16-byte-multiple
+ * rows) or by a cp.async ring (any shape).  on = 0 forces the cp.async ring (tests, comparisons). */
+void b200dp_head_fused_set_tma(int on);
 int b200dp_head_fused(const float* p2, int ld_p2, const float* w3, const float* b3, const float* w1, const float* b1,
                       const float* w2, const float* b2, const int64_t* target, int loss_mode, float* a3, int ld_a3,
                       float* h1, int ld_h1, float* probs, float* loss_rows, float* loss_out, float* dlogits,

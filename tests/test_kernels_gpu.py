@@ -139,10 +139,19 @@ def test_head_tail(mode, B, F1):
     assert int(acc[1]) == int(probs.argmax(1).eq(t).sum())
 
 
+@pytest.fixture(params=[1, 0], ids=["tma", "cp_async"])
+def head_weight_path(request):
+    """Both weight streams of the fused head: TMA tensor maps (default) and the cp.async ring."""
+    lib = _native().load()
+    lib.b200dp_head_fused_set_tma(request.param)
+    yield request.param
+    lib.b200dp_head_fused_set_tma(1)
+
+
 @pytest.mark.parametrize("mode", ["ref", "xent"])
-@pytest.mark.parametrize("B,K3,C3,F1,pitched", [(256, 400, 120, 84, False), (37, 400, 120, 84, True), (64, 150, 128, 128, True),
+@pytest.mark.parametrize("B,K3,C3,F1,pitched", [(256, 400, 120, 84, False), (37, 400, 120, 84, True), (64, 152, 128, 128, True),
                                                   (9, 33, 17, 5, False)])
-def test_head_fused(mode, B, K3, C3, F1, pitched):
+def test_head_fused(mode, B, K3, C3, F1, pitched, head_weight_path):
     """conv3 + FC.0 + FC.2 + softmax + loss + dlogits + dz1 + dz3 in one launch against fp64 autograd (cnn.py:16-23,
     train.py:48-49), dense and pitched buffers, ragged row blocks, eval counters."""
     native = _native()
