@@ -22,3 +22,8 @@ run 8 n8_oneshot --algo oneshot
 run 8 n8_bf16wire --wire bf16
 run 8 n8_strong --config strong4096
 fi
+if [ -n "$SWEEP" ]; then
+SWEEP_MAX_BYTES=4194304 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+    --master-port 29641 bench/allreduce_sweep.py > gpurun_out/sweep_n8.log 2>&1
+echo "sweep rc=$?"; grep '^{' gpurun_out/sweep_n8.log | cut -c1-400
+fi
