@@ -335,8 +335,8 @@ class NativeStepper:
                      if self.world > 1 else None)
         # One launch ends the step (wait for the peers' pushed gradients, sum, average, update the whole arena) when the
         # model is in the latency regime; big arenas keep one handshake launch per bucket (csrc/reduce_update.cu).
-        from ..parallel.p2p import LL_MAX_ARENA_BYTES
-        small = self.arena.layout.total * 4 <= LL_MAX_ARENA_BYTES
+        from ..parallel.p2p import ll_max_bytes
+        small = self.arena.layout.total * 4 <= ll_max_bytes(self.world)
         self.fused_final = (self.comm.push if self.comm is not None else (small and algo in ("auto", "push")))
         self.use_graph, self.overlap = graph, overlap
         self.side = torch.cuda.Stream(device=self.device) if overlap else None

@@ -107,7 +107,7 @@ class DataParallel(nn.Module):
     # -- native (sm_100a) state ------------------------------------------------
     def _init_native(self, algo: str, wire: str, timeout_ms: int) -> None:
         from ..ops import native
-        from .p2p import LL_MAX_ARENA_BYTES, P2PComm
+        from .p2p import P2PComm, ll_max_bytes
         native.load()
         self._nat = native
         dev = self.arena.param.device
@@ -115,7 +115,7 @@ class DataParallel(nn.Module):
         with torch.cuda.device(dev):
             self.p2p = (P2PComm(self.arena.layout.total, rank, self.world_size, algo, wire=wire, timeout_ms=timeout_ms)
                         if self.world_size > 1 else None)
-        small = self.arena.layout.total * 4 <= LL_MAX_ARENA_BYTES
+        small = self.arena.layout.total * 4 <= ll_max_bytes(self.world_size)
         self.push = self.p2p.push if self.p2p is not None else (small and algo in ("auto", "push"))
         self.side = torch.cuda.Stream(device=dev)
         self.hyper_dev = torch.zeros(8, dtype=torch.float32, device=dev)

@@ -48,6 +48,14 @@ WIRE_CODES = {"fp32": 0, "bf16": 1}
 # travel with a 4-byte flag) and keeps a receive area of 128 bytes per arena float on every rank; beyond ~1 MB the
 # handshake kernels, which move (world-1)/world .. (world-1) x arena bytes, are the better trade.
 LL_MAX_ARENA_BYTES = 1 << 20
+
+
+def ll_max_bytes(world: int) -> int:
+    """Largest arena the push protocol is chosen for by ``algo="auto"``.  Measured cross-over against the one-shot
+    handshake kernel as ISOLATED launches (profiles/allreduce_sweep.md): 2 ranks 10-12 us up to 1 MB (one-shot 12-23);
+    8 ranks 11-13 us up to 64 KB, level at 256 KB (21.5 vs 20.5), behind at 1 MB (63 vs 35: 14 MB leave every rank).
+    Inside a training step the early buckets' pushes overlap the backward pass, which favours the push protocol further."""
+    return max(256 << 10, (2 << 20) // max(world, 1))
 # Measured cross-over (profiles/allreduce_sweep.md).  One-shot pulls (world-1) x bytes into every rank but needs a
 # single handshake; two-shot / NVLS move 2(world-1)/world x bytes with two.  With 2 ranks the byte counts are
 # equal, so one-shot always wins; at 8 ranks it wins up to ~2 MB (1 MB: 35 vs 39 us, 4 MB: 70 vs 45 us NVLS).
@@ -71,7 +79,7 @@ class P2PComm:
         self.flag_off = (self.stage_bytes + 255) // 256 * 256
         flags_end = self.flag_off + (MAX_WORLD + 1) * self.max_slices * 4
         # receive area of the push protocol (only for arenas in the latency regime, or when asked for)
-        self.ll_enabled = algo == "push" or (algo == "auto" and arena_len * 4 <= LL_MAX_ARENA_BYTES)
+        self.ll_enabled = algo == "push" or (algo == "auto" and arena_len * 4 <= ll_max_bytes(world))
         self.ll_off = (flags_end + 255) // 256 * 256
         self.ll_bytes = 2 * MAX_WORLD * arena_len * 2 * 4 if self.ll_enabled else 0
         self.total_bytes = self.ll_off + self.ll_bytes
