@@ -24,6 +24,8 @@
 // the MMAs (uniform control flow, one elected lane), warps 0-3 run the epilogue.
 #include <cuda_bf16.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -299,8 +301,10 @@ using namespace b200dp;
 extern "C" void b200dp_tcw_wgrad_set_debug(long long* dbg) { g_wg_dbg = dbg; }
 
 extern "C" int b200dp_tcw_conv_wgrad_num_partials(b200dp_dims d) {
-    int n = (d.batch + 1) / 2;
-    if (n > 128) n = 128;
+    static const int ipc = getenv("B200DP_EXP_WG_IPC") ? atoi(getenv("B200DP_EXP_WG_IPC")) : 2;
+    int n = (d.batch + ipc - 1) / ipc;
+    const int cap = ipc == 1 ? 256 : 128;
+    if (n > cap) n = cap;
     return n < 1 ? 1 : n;
 }
 
