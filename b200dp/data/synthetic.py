@@ -111,6 +111,7 @@ class PinnedRingLoader:
         assert fmt in ("u8", "f32", "pre")
         assert (images.dtype == torch.float32) == (fmt == "pre"), "fmt 'pre' <=> float32 base array"
         self.max_batches = max_batches
+        self._order_ahead = None
         self.images, self.targets = images, targets
         self.start, self.stop = int(start), int(stop)
         self.batch_size = int(batch_size)
@@ -159,12 +160,31 @@ class PinnedRingLoader:
         nb = n // self.batch_size if self.drop_last else math.ceil(n / self.batch_size)
         return nb if self.max_batches is None else min(nb, self.max_batches)
 
-    def _order(self) -> torch.Tensor:
+    def _order_for(self, epoch: int) -> torch.Tensor:
         n = self.stop - self.start
         if self.shuffle:
-            g = torch.Generator().manual_seed(self.seed * 1_000_003 + self.epoch)
+            g = torch.Generator().manual_seed(self.seed * 1_000_003 + epoch)
             return torch.randperm(n, generator=g) + self.start
         return torch.arange(self.start, self.stop)
+
+    def _order(self) -> torch.Tensor:
+        """This epoch's sample order (a fresh permutation per epoch, train.py:83 ``shuffle=True``).  The NEXT epoch's
+        permutation is computed on a background thread meanwhile: for a 60,000-sample shard it takes milliseconds, which
+        would otherwise sit at the start of every epoch with the GPU idle."""
+        import threading
+        epoch = self.epoch
+        pending = self._order_ahead
+        if pending is not None and pending[0] == epoch:
+            pending[1].join()
+            order = pending[2][0]
+        else:
+            order = self._order_for(epoch)
+        if self.shuffle and self.stop - self.start >= 32768:      # small shards: cheaper to permute inline than to start a thread
+            box = [None]
+            th = threading.Thread(target=lambda: box.__setitem__(0, self._order_for(epoch + 1)), daemon=True)
+            th.start()
+            self._order_ahead = (epoch + 1, th, box)
+        return order
 
     def _stage(self, slot: int, idx: torch.Tensor) -> int:
         b = idx.numel()

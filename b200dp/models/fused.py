@@ -353,6 +353,7 @@ class NativeStepper:
         self._comm_off = False        # measurement aid: see set_comm_enabled
         self._loss_posted = False
         self._eval_graphs, self._eval_warm = 0, False
+        self._flag_stream, self._flag_host = None, None
         self._pumps = []
         hf = self.net.head_fused
         n = (3 if hf else 5) + (1 if self.net.conv_tc else 0) + (1 if hf else 2) + (3 if self.net.convbwd_tc else 1)
@@ -559,10 +560,21 @@ class NativeStepper:
             self.comm.reset()
 
     def error_flag(self) -> int:
-        """The device's sticky error word (one D2H read; call at points that synchronise anyway)."""
-        return int(self.step_counter[2].item())
+        """The device's sticky error word, read WITHOUT waiting for the queued steps: a 4-byte copy on a stream of its
+        own (a `.item()` on the compute stream at every log point drained the step pump's queue: one pipeline bubble
+        per log interval, several us per step at short intervals).  The word is sticky, so a value that is one chunk
+        old only delays the report by a log interval."""
+        if self._flag_stream is None:
+            self._flag_stream = torch.cuda.Stream(device=self.device)
+            self._flag_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        with torch.cuda.stream(self._flag_stream):
+            self._flag_host.copy_(self.step_counter[2:3], non_blocking=True)
+        self._flag_stream.synchronize()
+        return int(self._flag_host[0])
 
     def check_error(self) -> None:
+        """Raise if a peer did not deliver (synchronises with the compute stream first: for the end of a run / tests)."""
+        torch.cuda.current_stream(self.device).synchronize()
         if self.error_flag() != 0:
             raise RuntimeError("a peer rank did not deliver its gradients within the time bound (dead or stalled "
                                "rank?); this rank stopped updating its parameters at that step")
