@@ -437,11 +437,16 @@ class NativeStepper:
                     return
                 if not last and (self.comm is None or self._comm_off):
                     return                           # nothing to send at world size 1
+                if last:
+                    # the step's final launch runs on the MAIN stream, right behind the last backward kernel (programmatic
+                    # dependent launch: its CTAs are resident when that kernel drains), after joining the side stream: the
+                    # pushes and the loss post read the generation this launch advances
+                    main.wait_stream(side)
+                    self._final_update(pushed=True)
+                    return
                 side.wait_stream(main)
                 with torch.cuda.stream(side):
-                    if last:
-                        self._final_update(pushed=True)
-                    elif both:
+                    if both:
                         self._push_range(bk[1].start, bk[0].stop - bk[1].start)
                     else:
                         self._push(i)

@@ -155,6 +155,7 @@ __global__ void __launch_bounds__(LL_NT) grad_push_kernel(const float* grad, int
 }
 
 __global__ void __launch_bounds__(LL_NT, 2) reduce_update_ll_kernel(LLArgs a) {
+    pdl_wait();      // launched with programmatic serialization behind the last backward kernel (no-op otherwise)
     __shared__ __align__(16) float sRed[8][128];
     __shared__ __align__(16) float sSlice[LL_PSLICE];
     const int tid = threadIdx.x;
@@ -308,7 +309,7 @@ extern "C" int b200dp_reduce_update_ll(float* param, float* grad, float* state0,
     if (rest < 1 && a.n_chunks > 0) rest = 1;
     const int grid = a.n_pcta + rest;
     B200DP_REQUIRE(grid > 0, "empty launch");
-    reduce_update_ll_kernel<<<grid, LL_NT, 0, (cudaStream_t)s>>>(a);
+    B200DP_CHECK(launch_pdl(reduce_update_ll_kernel, dim3(grid), dim3(LL_NT), 0, (cudaStream_t)s, a));
     B200DP_CHECK(cudaGetLastError());
     return 0;
 }
