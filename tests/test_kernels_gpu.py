@@ -309,6 +309,63 @@ def test_reduce_update_matches_flat_optimizer(kind):
         assert torch.allclose(s0, ref.state0, atol=1e-7, rtol=1e-5)
 
 
+@pytest.mark.parametrize("kind", ["adadelta", "sgd", "adam"])
+def test_reduce_update_ll_world1_matches_flat_optimizer(kind):
+    """The push protocol's final kernel without peers: whole-arena update in one launch, a sub-range fed by partial
+    rows (fixed-order sum), bf16 shadow weights, generation counter — against the torch flat optimizer."""
+    native = _native()
+    from b200dp.optim.flat import FlatOptimizer, OptHyper
+    torch.manual_seed(6)
+    dev = "cuda"
+    n, p_start, p_count, rows = 4096 + 640, 1024, 512, 37
+    p0 = torch.randn(n, device=dev)
+    hyper = OptHyper(kind, lr=0.05, weight_decay=0.01 if kind == "sgd" else 0.0)
+    ref = FlatOptimizer(p0.clone(), torch.zeros(n, device=dev), hyper)
+    p, g = p0.clone(), torch.zeros(n, device=dev)
+    s0, s1 = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    shadow = torch.zeros(n, dtype=torch.bfloat16, device=dev)
+    hv = torch.tensor(list(ref.hyper_vector()) + [0, 0, 0], dtype=torch.float32, device=dev)
+    counter = torch.zeros(4, dtype=torch.int32, device=dev)
+    for step in range(4):
+        grad = torch.randn(n, device=dev) * 0.1
+        partials = torch.randn(rows, p_count, device=dev) * 0.02
+        grad[p_start:p_start + p_count] = partials.double().sum(0).float()
+        ref.grad.copy_(grad)
+        ref.step_torch()
+        g.copy_(grad)
+        g[p_start:p_start + p_count] = float("nan")          # that range must come from the rows, not from the arena
+        native.reduce_update_ll(p, g, s0, s1, shadow, 0, n, partials, rows, p_count, p_start, p_count, False,
+                                hyper.code(), hv, counter, None)
+        torch.cuda.synchronize()
+        assert int(counter[0]) == step + 1 and int(counter[2]) == 0
+        assert torch.allclose(p, ref.param, atol=2e-6, rtol=1e-5), (kind, step, (p - ref.param).abs().max())
+        assert torch.allclose(s0, ref.state0, atol=1e-6, rtol=1e-5)
+        assert torch.allclose(g, grad, atol=1e-6)            # the averaged gradient is written back (train.py:39)
+        assert torch.equal(shadow, p.to(torch.bfloat16))     # round-to-nearest-even copy for tensor-core consumers
+
+
+def test_post_loss_and_fetch_slot():
+    """The two small kernels of the step pump: the loss into a mapped pinned array at slot (generation - base), and
+    the upload of a pinned ring slot by a kernel that reads host memory through its mapped address."""
+    native = _native()
+    dev = "cuda"
+    ring = torch.full((8,), -1.0).pin_memory()
+    loss = torch.tensor([0.625], device=dev)
+    counter = torch.zeros(4, dtype=torch.int32, device=dev)
+    counter[0] = 41                                              # 41 steps done: the running step has generation 42
+    sink = torch.tensor([ring.data_ptr(), 40, ring.numel(), 0], dtype=torch.int64, device=dev)
+    native.post_loss(loss, counter, sink)
+    sink_off = torch.tensor([ring.data_ptr(), 50, ring.numel(), 0], dtype=torch.int64, device=dev)
+    native.post_loss(loss, counter, sink_off)                    # slot would be negative: nothing is written
+    torch.cuda.synchronize()
+    assert ring[2] == 0.625 and (ring[:2] == -1).all() and (ring[3:] == -1).all()
+    src = torch.randint(0, 256, (200704 + 2048,), dtype=torch.uint8).pin_memory()
+    dst = torch.zeros_like(src, device=dev)
+    native.fetch_slot(dst, src)
+    torch.cuda.synchronize()
+    assert torch.equal(dst.cpu(), src)
+
+
 def test_reduce_update_partials_deterministic():
     native = _native()
     torch.manual_seed(7)
