@@ -43,9 +43,13 @@ struct WgCfg {
     static constexpr int KGA = (CA + 7) / 8;                          // groups of 8 bf16 channels (16 bytes)
     static_assert(CA <= 128, "expanded channels must fit the 128 accumulator rows");
     static constexpr int NP = (COUT + 15) / 16 * 16, KGB = NP / 8;
-    static constexpr int NPOS = ((OW - 1) * PITCH + OW + 15) / 16 * 16;  // K extent of one image (16 positions per MMA)
-    static constexpr int P = FIRST ? 128 : NPOS;                      // positions per chunk
-    static constexpr int NCHUNK = (NPOS + P - 1) / P;
+    static constexpr int POS16 = ((OW - 1) * PITCH + OW + 15) / 16 * 16;  // K extent of one image (16 positions per MMA)
+    // positions per chunk.  The chunk pipeline is a round trip per chunk (stage -> MMAs -> completion frees the buffer) and
+    // with two buffers that round trip, not the staging work, sets the pace: 256-position chunks where shared memory
+    // allows two such buffers (single input channel) instead of 128 took the reference LeNet's conv1 wgrad from 11.8 us down
+    static constexpr int P = FIRST ? (CIN == 1 ? 256 : 128) : POS16;
+    static constexpr int NPOS = (POS16 + P - 1) / P * P;              // B holds whole chunks: no MMA reads past its end
+    static constexpr int NCHUNK = NPOS / P;
     static constexpr int TAP_SPAN = FIRST ? 0 : 4 * PITCH;
     static constexpr int PA = P + TAP_SPAN;                           // positions held by the A buffer
     static constexpr int A_BYTES = 16 * PA * 16;                      // M = 128 addresses 16 channel groups of 8
