@@ -357,7 +357,7 @@ class NativeStepper:
         self._pumps = []
         hf = self.net.head_fused
         n = (3 if hf else 5) + (1 if self.net.conv_tc else 0) + (1 if hf else 2) + (3 if self.net.convbwd_tc else 1)
-        pushes = 0 if self.world == 1 else (1 if hf else 2)
+        pushes = 1 if hf else (0 if self.world == 1 else 2)      # fused head: one dense push+wait+update launch
         n += (1 + pushes) if self.fused_final else 3                                       # reduce/update (+ pushes)
         n += 1 if overlap else 0                                                            # post_loss beside the backward
         self.launches_per_step = n            # forward + GEMM backward + conv backward + gradient exchange/update
@@ -399,16 +399,27 @@ class NativeStepper:
         if cs is not None:
             native.grad_push(self.arena.grad, start, count, self.step_counter, cs)
 
-    def _final_update(self, pushed: bool) -> None:
-        """Push protocol: the step's single wait + sum + average + update launch over the whole arena; it sums the
-        convolution backward's partial rows and pushes that bucket itself."""
+    def _final_update(self, pushed: bool, conv_only: bool = False) -> None:
+        """Push protocol: the step's last launch — sums the convolution backward's partial rows, pushes that bucket,
+        waits for the peers' lines, sums in rank order, averages, updates.  Over the whole arena, or (``conv_only``) over
+        the convolution bucket alone when the dense buckets had their own launch beside the convolution backward."""
         net, opt = self.net, self.optimizer
         conv = self.arena.layout.buckets[2]
-        native.reduce_update_ll(self.arena.param, self.arena.grad, opt.state0, opt.state1, None, 0,
-                                self.arena.layout.total, net.partials, net.cur_partials, net.partial_stride,
-                                conv.start, conv.numel, not pushed, opt.hyper.code(), self.hyper_dev,
-                                self.step_counter, self._comm_struct(0, False), net.loss,
-                                None if self._loss_posted else self.loss_sink)
+        start, count = (conv.start, conv.numel) if conv_only else (0, self.arena.layout.total)
+        native.reduce_update_ll(self.arena.param, self.arena.grad, opt.state0, opt.state1, None, start, count,
+                                net.partials, net.cur_partials, net.partial_stride, conv.start, conv.numel, not pushed,
+                                opt.hyper.code(), self.hyper_dev, self.step_counter, self._comm_struct(0, False), net.loss,
+                                None if self._loss_posted else self.loss_sink, last=True)
+
+    def _dense_update(self, start: int, count: int) -> None:
+        """Push protocol, dense buckets (FC.*, conv3: 95 % of the gradient): ONE launch pushes them to every peer, waits
+        for the peers' lines and updates — on the side stream, beside the convolution backward, so that the step's last
+        launch only has the 10 KB convolution bucket left (at 8 GPUs gathering 7 peers' lines for the whole arena in the
+        last launch cost ~3 us of exposed time)."""
+        opt = self.optimizer
+        native.reduce_update_ll(self.arena.param, self.arena.grad, opt.state0, opt.state1, None, start, count, None, 0, 0,
+                                0, 0, True, opt.hyper.code(), self.hyper_dev, self.step_counter,
+                                self._comm_struct(0, False), None, None, last=False)
 
     def _step_body(self, x: torch.Tensor, y: torch.Tensor) -> None:
         main = torch.cuda.current_stream(self.device)
@@ -435,19 +446,19 @@ class NativeStepper:
                     if last:
                         self._final_update(pushed=False)
                     return
-                if not last and (self.comm is None or self._comm_off):
-                    return                           # nothing to send at world size 1
                 if last:
                     # the step's final launch runs on the MAIN stream, right behind the last backward kernel (programmatic
                     # dependent launch: its CTAs are resident when that kernel drains), after joining the side stream: the
                     # pushes and the loss post read the generation this launch advances
                     main.wait_stream(side)
-                    self._final_update(pushed=True)
+                    self._final_update(pushed=True, conv_only=both)
                     return
+                if not both and (self.comm is None or self._comm_off):
+                    return                           # nothing to send at world size 1
                 side.wait_stream(main)
                 with torch.cuda.stream(side):
-                    if both:
-                        self._push_range(bk[1].start, bk[0].stop - bk[1].start)
+                    if both:                         # push + wait + update of the dense buckets, beside the conv backward
+                        self._dense_update(bk[1].start, bk[0].stop - bk[1].start)
                     else:
                         self._push(i)
                 return

@@ -103,7 +103,7 @@ def load(build_if_missing: bool = True):
     lib.b200dp_conv_bwd.argtypes = [vp, i, f, f, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, Dims, vp]
     lib.b200dp_reduce_update.argtypes = [vp, vp, vp, vp, vp, i, i, vp, i, i, i, vp, vp, i, C.POINTER(Comm), vp, vp, vp]
     lib.b200dp_grad_push.argtypes = [vp, i, i, vp, C.POINTER(Comm), vp]
-    lib.b200dp_reduce_update_ll.argtypes = [vp, vp, vp, vp, vp, i, i, vp, i, i, i, i, i, i, vp, vp, C.POINTER(Comm), vp, vp, vp]
+    lib.b200dp_reduce_update_ll.argtypes = [vp, vp, vp, vp, vp, i, i, vp, i, i, i, i, i, i, i, vp, vp, C.POINTER(Comm), vp, vp, vp]
     lib.b200dp_post_loss.argtypes = [vp, vp, vp, vp]
     lib.b200dp_symm_alloc.argtypes = [C.POINTER(vp), C.c_uint64]
     lib.b200dp_symm_free.argtypes = [vp]
@@ -307,11 +307,11 @@ def grad_push(grad, start: int, count: int, step_counter, comm: Comm) -> None:
 
 def reduce_update_ll(param, grad, state0, state1, shadow, start: int, count: int, partials, n_partials: int,
                      partial_stride: int, p_start: int, p_count: int, push_rest: bool, opt_kind: int, hyper,
-                     step_counter, comm: Optional[Comm], loss_src=None, loss_sink=None) -> None:
+                     step_counter, comm: Optional[Comm], loss_src=None, loss_sink=None, last: bool = True) -> None:
     """The step's single wait + rank-order sum + average + optimizer launch of the push protocol."""
     check(load().b200dp_reduce_update_ll(_p(param), _p(grad), _p(state0), _p(state1), _p(shadow), start, count,
                                          _p(partials), n_partials, partial_stride, p_start, p_count, int(push_rest),
-                                         opt_kind, _p(hyper), _p(step_counter),
+                                         int(last), opt_kind, _p(hyper), _p(step_counter),
                                          C.byref(comm) if comm is not None else None, _p(loss_src), _p(loss_sink),
                                          _stream()), "reduce_update_ll")
 

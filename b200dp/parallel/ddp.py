@@ -217,7 +217,7 @@ class DataParallel(nn.Module):
             self._on_side(lambda: self._nat.reduce_update_ll(
                 self.arena.param, self.arena.grad, opt.state0, opt.state1, None, 0, self.arena.layout.total, None, 0, 0,
                 0, 0, all_here, opt.hyper.code(), self.hyper_dev, self.step_counter,
-                self.p2p.struct_for(0) if self.p2p else None))
+                self.p2p.struct_for(0) if self.p2p else None, last=True))
         else:
             rest = [bi for bi in range(nb) if not self._sent[bi]]
             for k, bi in enumerate(rest):

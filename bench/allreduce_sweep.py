@@ -92,7 +92,7 @@ def main():
             st_ll = comm_ll.struct_for(0)
 
             def push_step():   # one launch: push + wait + rank-order sum + average + momentum update
-                native.reduce_update_ll(param, grad, s0, s1, None, 0, n, None, 0, 0, 0, 0, True, OPT_SGD, hyper, counter, st_ll)
+                native.reduce_update_ll(param, grad, s0, s1, None, 0, n, None, 0, 0, 0, 0, True, OPT_SGD, hyper, counter, st_ll, last=True)
             rec["push_us"] = timed(push_step, iters)
             rec["push_roofline_frac"] = (2 * (world - 1) * n * 4 / (LINK_GBS * 1e9)) / (rec["push_us"] * 1e-6)
         if int(counter[2]) != 0:

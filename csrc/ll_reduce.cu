@@ -49,6 +49,7 @@ struct LLArgs {
     const float* partials; int n_partials, partial_stride;
     int p_start, p_count;              // sub-range whose local gradient is the sum of the partial rows (p_count 0: none)
     int push_rest;                     // 1: this launch also pushes the rest of the range (nobody called grad_push)
+    int last;                          // 1: the step's last launch (advances the generation, takes the completion ticket)
     int opt_kind;
     const float* hyper;
     uint32_t* step_counter;
@@ -224,7 +225,7 @@ __global__ void __launch_bounds__(LL_NT, 2) reduce_update_ll_kernel(LLArgs a) {
             }
         }
     }
-    ru_finish_step(a.step_counter, gen, gridDim.x, a.loss_src, a.loss_sink, tid);
+    if (a.last) ru_finish_step(a.step_counter, gen, gridDim.x, a.loss_src, a.loss_sink, tid);
 }
 
 }  // namespace b200dp
@@ -270,7 +271,7 @@ extern "C" int b200dp_grad_push(const float* grad, int start, int count, const u
 
 extern "C" int b200dp_reduce_update_ll(float* param, float* grad, float* state0, float* state1, uint16_t* shadow_bf16,
                                        int start, int count, const float* partials, int n_partials,
-                                       int partial_stride, int p_start, int p_count, int push_rest, int opt_kind,
+                                       int partial_stride, int p_start, int p_count, int push_rest, int last, int opt_kind,
                                        const float* hyper, uint32_t* step_counter, const b200dp_comm* comm,
                                        const float* loss_src, const uint64_t* loss_sink, b200dp_stream_t s) {
     B200DP_REQUIRE(start % 4 == 0 && count % 4 == 0 && count > 0, "range must be float4-aligned");
@@ -288,7 +289,7 @@ extern "C" int b200dp_reduce_update_ll(float* param, float* grad, float* state0,
     a.param = param; a.grad = grad; a.state0 = state0; a.state1 = state1; a.shadow = shadow_bf16;
     a.start = start; a.count = count;
     a.partials = partials; a.n_partials = n_partials; a.partial_stride = partial_stride;
-    a.p_start = p_start; a.p_count = p_count; a.push_rest = push_rest;
+    a.p_start = p_start; a.p_count = p_count; a.push_rest = push_rest; a.last = last;
     a.opt_kind = opt_kind; a.hyper = hyper; a.step_counter = step_counter;
     a.loss_src = loss_src; a.loss_sink = loss_src ? (const unsigned long long*)loss_sink : nullptr;
     if (comm && comm->world > 1) {

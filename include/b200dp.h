@@ -277,15 +277,17 @@ int b200dp_reduce_update(float* param, float* grad, float* state0, float* state1
  *                            partials NULL / p_count 0: none) and pushes that sub-range itself, pushes the rest
  *                            too when push_rest != 0 (nobody called b200dp_grad_push this step), then for every
  *                            element waits for the peers' lines in LOCAL memory, adds in rank order, scales by
- *                            1/world, applies the optimizer, advances the generation (always the step's last
- *                            launch) and delivers the loss (loss_src / loss_sink as in b200dp_reduce_update).
+ *                            1/world, applies the optimizer and, when last != 0 (the step's last launch), advances the
+ *                            generation and delivers the loss (loss_src / loss_sink as in b200dp_reduce_update).  A step
+ *                            may split its arena over several launches on disjoint ranges (e.g. the dense layers'
+ *                            buckets beside the convolution backward, the convolution bucket at the end).
  * comm may be NULL (or world 1): plain local update.  A wait that exceeds comm->timeout_ms raises the sticky
  * error word step_counter[2]; from then on every launch of either protocol only does its bookkeeping. */
 int b200dp_grad_push(const float* grad, int start, int count, const uint32_t* step_counter,
                      const b200dp_comm* comm, b200dp_stream_t s);
 int b200dp_reduce_update_ll(float* param, float* grad, float* state0, float* state1, uint16_t* shadow_bf16,
                             int start, int count, const float* partials, int n_partials, int partial_stride,
-                            int p_start, int p_count, int push_rest, int opt_kind, const float* hyper,
+                            int p_start, int p_count, int push_rest, int last, int opt_kind, const float* hyper,
                             uint32_t* step_counter, const b200dp_comm* comm, const float* loss_src,
                             const uint64_t* loss_sink, b200dp_stream_t s);
 
