@@ -1,19 +1,18 @@
 """Native LeNet runner: the whole training step as a short fixed sequence of
 hand-written sm_100a kernels over flat arenas, replayed from a CUDA graph.
 
-Default step for the reference LeNet = 9 launches (+1 push with more than one GPU); reference: ~50 ATen/cuDNN/cuBLAS
-kernels + 10 NCCL all-reduces + 10 divides + the optimizer's elementwise kernels, train.py:45-51:
+Default step for the reference LeNet = 11 launches, 7 of them on the main stream's dependency chain; reference: ~50
+ATen/cuDNN/cuBLAS kernels + 10 NCCL all-reduces + 10 divides + the optimizer's elementwise kernels, train.py:45-51:
 
     main stream                                                      other streams (overlapped)
-    ---------------------------------------------------------------  ------------------------------------------
+    ---------------------------------------------------------------  ------------------------------------------------
     conv1 fwd   (normalise+upsample+conv+act+pool)   CUDA cores      tcw_pack_weights (bf16 panels)
     conv2 fwd   (conv+act+pool)                      tcgen05 bf16
-    head_fused  (conv3+FC.0+FC.2+softmax+loss+dlogits+dz1+dz3) fp32
-    tc_gemm     {dW FC.2, dW FC.0, dW conv3, dP2}    tcgen05 tf32    grad_push of the two dense buckets (world > 1)
-    conv2 dgrad (pool/act bwd fused)                 tcgen05 bf16    conv2 wgrad (tcgen05 bf16)
-    conv1 wgrad                                      tcgen05 bf16
-                                                                     reduce_update_ll: partial rows + push + wait +
-                                                                     rank-order sum + average + optimizer, whole arena
+    head_fused  (conv3+FC.0+FC.2+softmax+loss+dlogits+dz1+dz3) fp32, weights by TMA
+    tc_gemm     {dW FC.2, dW FC.0, dW conv3, dP2}    tcgen05 tf32    post_loss (loss -> host's mapped array)
+    conv2 dgrad (pool/act bwd fused)                 tcgen05 bf16    reduce_update_ll, dense buckets: push to peers + wait +
+    conv1 wgrad                                      tcgen05 bf16      rank-order sum + average + optimizer;  conv2 wgrad
+    reduce_update_ll, conv bucket (the step's last launch: partial rows + push + wait + sum + average + optimizer)
 
 Which kernel runs a layer is a measured choice (``dtype="auto"``, ``conv="auto"``; profiles/lenet_tc_vs_simt.md): conv1
 (K = 25) is faster on CUDA cores, everything from conv2 on is faster on the tensor cores; ``dtype="fp32", conv="simt"``
@@ -393,11 +392,6 @@ class NativeStepper:
         if cs is not None:
             b = self.arena.layout.buckets[bucket_index]
             native.grad_push(self.arena.grad, b.start, b.numel, self.step_counter, cs)
-
-    def _push_range(self, start: int, count: int) -> None:
-        cs = self._comm_struct(0, False)
-        if cs is not None:
-            native.grad_push(self.arena.grad, start, count, self.step_counter, cs)
 
     def _final_update(self, pushed: bool, conv_only: bool = False) -> None:
         """Push protocol: the step's last launch — sums the convolution backward's partial rows, pushes that bucket,
