@@ -50,8 +50,8 @@ class StepPump:
         self._graphs = []
         self._handle: Optional[int] = None
         self._loss_keepalive = None
-        self._sink_host = torch.zeros(4, dtype=torch.int64)
         self._sink_stage = [torch.zeros(4, dtype=torch.int64).pin_memory() for _ in range(8)]   # in-flight H2D sources
+        self._sink_np = [t.numpy() for t in self._sink_stage]
         self._sink_i = 0
 
     # graphs are captured lazily: the stepper wants two eager steps first (lazy module loading)
@@ -120,15 +120,14 @@ class StepPump:
         self._ensure_graphs()
         st._sync_hyper()
         n = n_steps - k0
-        # tell the device where this run's losses go: {array, generation of its element 0, length}
+        # tell the device where this run's losses go: {array, generation of its element 0, length} — written straight into
+        # a pinned staging vector (one numpy store, one small H2D copy; a ring of vectors because the copies are in flight)
+        stage = self._sink_np[self._sink_i]
         if loss_host is not None:
             assert loss_host.dtype == torch.float32 and not loss_host.is_cuda and loss_host.numel() >= n_steps
-            self._sink_host[0] = loss_host.data_ptr() + 4 * k0
-            self._sink_host[1] = st.optimizer.step_count + 1
-            self._sink_host[2] = n
+            stage[:3] = (loss_host.data_ptr() + 4 * k0, st.optimizer.step_count + 1, n)
         else:
-            self._sink_host.zero_()
-        self._sink_stage[self._sink_i].copy_(self._sink_host)
+            stage[:3] = 0
         st.loss_sink.copy_(self._sink_stage[self._sink_i], non_blocking=True)
         self._sink_i = (self._sink_i + 1) % len(self._sink_stage)
         st.optimizer.step_count += n

@@ -179,12 +179,27 @@ class PinnedRingLoader:
             order = pending[2][0]
         else:
             order = self._order_for(epoch)
-        if self.shuffle and self.stop - self.start >= 32768:      # small shards: cheaper to permute inline than to start a thread
+        if self.shuffle and self.stop - self.start >= 32768:      # small shards: see prepare_next
             box = [None]
             th = threading.Thread(target=lambda: box.__setitem__(0, self._order_for(epoch + 1)), daemon=True)
             th.start()
             self._order_ahead = (epoch + 1, th, box)
         return order
+
+    def prepare_next(self) -> None:
+        """Small shards: permute the NEXT epoch inline, now.  The training loop calls this once an epoch's last steps are
+        queued and the GPU is still busy with them, so the permutation never sits at an epoch's start."""
+        if not self.shuffle:
+            return
+        nxt = self.epoch                       # the caller has advanced the epoch counter already
+        if self._order_ahead is not None and self._order_ahead[0] == nxt:
+            return                             # a background thread is on it (large shard) or it is done
+
+        class _Done:
+            @staticmethod
+            def join():
+                return None
+        self._order_ahead = (nxt, _Done, [self._order_for(nxt)])
 
     def _stage(self, slot: int, idx: torch.Tensor) -> int:
         b = idx.numel()

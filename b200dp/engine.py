@@ -226,6 +226,7 @@ class Trainer:
             if n_full % self.log_interval == 0 and self.ctx.is_main:
                 last = float(loss.item())
                 self.log.print(train_line(epoch, n_full, len(x), len(loader.dataset), n_batches, last))
+        loader.prepare_next()          # next epoch's sample order, while the GPU works through the queued steps
         pump.drain()
         self.check_peers()
         return last

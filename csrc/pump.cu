@@ -159,11 +159,23 @@ extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_
     cudaStream_t st = (cudaStream_t)stream;
     const int depth = p->d.depth;
     nvtxRangePushA("b200dp.pump_run");
+    // The first two batches of a run are gathered HERE, on the launching thread: handing them to the helper costs two
+    // thread wake-ups (~30-50 us each) with the GPU idle at the start of every epoch / log interval.
+    const int inline_steps = n_steps < 2 ? n_steps : 2;
+    p->order = order;
+    for (int k = 0; k < inline_steps; ++k) {
+        const int sl = k % depth;
+        bool pend;
+        { std::lock_guard<std::mutex> lk(p->mu); pend = p->slot_pending[sl]; }
+        if (pend) B200DP_CHECK(cudaEventSynchronize(p->slot_ev[sl]));
+        p->gather(k);
+        std::lock_guard<std::mutex> lk(p->mu);
+        p->slot_pending[sl] = false;
+    }
     {
         std::lock_guard<std::mutex> lk(p->mu);
-        p->order = order;
         p->req = n_steps;
-        p->filled = 0;
+        p->filled = inline_steps;
         p->launched = 0;
         p->failed = false;
     }
