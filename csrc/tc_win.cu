@@ -64,6 +64,9 @@ struct WinCfg {
     static constexpr bool WIDE = COUT > 16;
     static constexpr int G = KIND == WIN_FWD1 ? (WIDE ? 2 : 1) : 2;     // images per CTA
     static constexpr int RING = KIND == WIN_FWD1 ? 5 : (KIND == WIN_FWD2 ? (WIDE ? 8 : 25) : (WIDE ? 4 : 25));
+    // all taps resident: the panels arrive with ONE bulk copy (25 copies of 512 bytes each paced the MMA issue loop of the
+    // reference geometry: the copy unit handles a small copy in ~300 cycles, one after the other)
+    static constexpr bool W_ONESHOT = RING >= NTAP;
     static constexpr int ACC_COLS = G * NT * NP;
     static constexpr int TMEM_COLS = ACC_COLS <= 32 ? 32 : (ACC_COLS <= 64 ? 64 : (ACC_COLS <= 128 ? 128 : (ACC_COLS <= 256 ? 256 : 512)));
     static_assert(ACC_COLS <= 512, "accumulators exceed tensor memory");
@@ -175,7 +178,7 @@ __device__ __forceinline__ void win_issue(uint32_t tmem, uint32_t s_img, uint32_
 #pragma unroll 1
     for (int t = 0; t < C::NTAP; ++t) {
         const int s = t % C::RING;
-        mbar_wait(bars + 8u * s, (t / C::RING) & 1);
+        if (!C::W_ONESHOT || t == 0) mbar_wait(bars + 8u * s, (t / C::RING) & 1);
         tc_fence_after();
         const uint64_t at = adesc0 + (uint64_t)C::tap_shift(t);                 // the address field counts 16-byte units
         const uint64_t bt = bdesc0 + (uint64_t)(s * (C::WB >> 4));
@@ -241,8 +244,14 @@ __global__ void __launch_bounds__(WIN_THREADS, 1) win_conv_kernel(const __grid_c
     };
     if (warp == WIN_WORKERS + WIN_NMMA) {
         // ================= weight ring producer (one lane): fill the ring while the images are staged =================
-        if (lane == 0)
-            for (int t = 0; t < C::RING && t < C::NTAP; ++t) load_tap(t);
+        if (lane == 0) {
+            if constexpr (C::W_ONESHOT) {
+                mbar_expect_tx(w_full(0), C::NTAP * C::WB);
+                tma_bulk_load(smem_u32(sW), a.wpack, C::NTAP * C::WB, w_full(0));
+            } else {
+                for (int t = 0; t < C::RING && t < C::NTAP; ++t) load_tap(t);
+            }
+        }
     } else if (warp < WIN_WORKERS) {
         // ================= stage the CTA's images =================
         for (int g = 0; g < nimg; ++g) {
