@@ -15,12 +15,17 @@
 // wait+sum+update kernel runs.  One fabric traversal, one exposed wait per step.
 //
 //   b200dp_grad_push         fire-and-forget: grad[start, start+count) -> every peer's receive area
-//   b200dp_reduce_update_ll  ends the step: (a) sums the conv-backward partial rows of one sub-range
-//                            and pushes that sub-range itself, (b) for every float4 of the range waits
-//                            for each peer's line(s), adds in rank order (bit-identical on all ranks),
-//                            (c) x 1/world, Adadelta / SGD / Adam on the fp32 master weights, averaged
-//                            gradient written back, optional bf16 shadow weights, (d) advances the
-//                            generation and delivers the loss to the host.
+//   b200dp_reduce_update_ll  for an arena range: (a) sums the conv-backward partial rows of one sub-range
+//                            and pushes that sub-range itself (and, push_rest, the rest of the range),
+//                            (b) for every float4 of the range waits for each peer's line(s), adds in
+//                            rank order (bit-identical on all ranks), (c) x 1/world, Adadelta / SGD / Adam
+//                            on the fp32 master weights, averaged gradient written back, optional bf16
+//                            shadow weights, (d) when it is the step's LAST launch: advances the generation
+//                            (and can deliver the loss to the host).
+//   b200dp_post_loss         one thread: the loss into the host's mapped array, beside the backward pass
+// The default LeNet step uses two b200dp_reduce_update_ll launches: the dense buckets (95 % of the bytes:
+// push + wait + update in one launch on a side stream, hidden behind the convolution backward) and, last,
+// the 10 KB convolution bucket on the main stream.  A step's one-way NVLink latency is paid once.
 //
 // Receive area of a rank: [2 parities][8 source ranks][arena_len x 2 words].  Parity = generation & 1:
 // a rank can be at most one step ahead of a peer (it needs the peer's lines of step g to finish step
@@ -32,7 +37,8 @@
 // A peer that never delivers: the poll is bounded by wall time (comm.timeout_ms); the CTA then raises
 // the sticky error word step_counter[2], skips its update, and STILL takes its completion ticket, so
 // the generation keeps advancing and every later launch sees the error word and does nothing but
-// bookkeeping.  The host checks the word at every log point (Trainer) and raises on all ranks.
+// bookkeeping.  The host reads the word at every log point and at epoch end (Trainer.check_peers, a 4-byte copy on
+// a stream of its own) and raises; ranks that are still alive time out on the raiser's next step.
 #include "opt_math.cuh"
 
 namespace b200dp {

@@ -171,3 +171,32 @@ def test_native_library_builds_for_sm100a():
     assert len(names) > 30
     missing = [n for n in sorted(names) if not hasattr(h, n)]
     assert not missing, missing
+
+
+def test_push_threshold_and_new_cli_flags():
+    """The push protocol's auto threshold shrinks with the world size (measured cross-overs, profiles/allreduce_sweep.md)
+    and always covers the reference LeNet; the round-2 flags parse and default to the measured choices."""
+    from b200dp.cli import parse_args
+    from b200dp.parallel.p2p import ll_max_bytes
+    lenet_bytes = 61952 * 4                                   # the reference model's padded arena
+    assert ll_max_bytes(2) == 1 << 20 and ll_max_bytes(8) == 256 << 10
+    assert all(ll_max_bytes(w) >= lenet_bytes for w in range(1, 9))
+    a = parse_args([])
+    assert (a.wire, a.conv, a.peer_timeout_ms, a.allreduce_algo, a.data_root) == ("auto", "auto", 0, "auto", None)
+    a = parse_args(["--wire", "bf16", "--conv", "hybrid", "--peer-timeout-ms", "500", "--allreduce-algo", "push",
+                    "--data-root", "/tmp/x", "--dtype", "bf16"])
+    assert (a.wire, a.conv, a.peer_timeout_ms, a.allreduce_algo, a.data_root, a.dtype) == ("bf16", "hybrid", 500, "push", "/tmp/x", "bf16")
+
+
+def test_loader_prepares_next_epoch_order():
+    """Epoch orders are the same permutations whether they were prepared ahead (thread for large shards, inline
+    ``prepare_next`` for small ones) or computed on demand."""
+    import torch
+    from b200dp.data.synthetic import MNIST_SPEC, PinnedRingLoader, SyntheticImages
+    ds = SyntheticImages(300, MNIST_SPEC, seed=0)
+    mk = lambda: PinnedRingLoader(ds.images, ds.targets, 10, 290, 32, MNIST_SPEC, fmt="f32", seed=4)   # noqa: E731
+    a, b = mk(), mk()
+    for _ in range(3):
+        oa = a._order(); a.epoch += 1; a.prepare_next()        # what the pumped training loop does
+        ob = b._order_for(b.epoch); b.epoch += 1               # on demand
+        assert torch.equal(oa, ob) and sorted(oa.tolist()) == list(range(10, 290))
