@@ -37,6 +37,16 @@ import torch.distributed as dist
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner to fd 1 on the first
+# collective), so the real stdout is kept aside for the result line and fd 1 is pointed at stderr for everything else.
+_RESULT_OUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def _emit(obj):
+    print(json.dumps(obj), file=_RESULT_OUT, flush=True)
+
+
 PER_GPU_BATCH = 256
 L2_BYTES = 126 * 1024 * 1024
 
@@ -253,7 +263,7 @@ def run_own(args):
             "exposed_comm_us_per_step": exposed_us,
             "native_lib": os.path.relpath(native.lib_path(), ROOT),
         }
-        print(json.dumps(out), flush=True)
+        _emit(out)
     stepper.close()
     if dist.is_initialized():
         dist.destroy_process_group()
@@ -286,10 +296,10 @@ class _RefLoader:
 def run_reference(args):
     ref_dir = os.path.join(ROOT, "baseline", "_ref")
     if not os.path.isfile(os.path.join(ref_dir, "train.py")):
-        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref not installed (see DESIGN.md)"}))
+        _emit({"impl": "reference", "unavailable": "baseline/_ref not installed (see DESIGN.md)"})
         return
     if args.config != "lenet_b256":
-        print(json.dumps({"impl": "reference", "unavailable": "the reference has a single fixed model/config"}))
+        _emit({"impl": "reference", "unavailable": "the reference has a single fixed model/config"})
         return
     rank, world, local, dev = _init_dist(args.gpus)
     if not dist.is_initialized():   # the reference's average_gradients() needs a group even at size 1
@@ -323,7 +333,7 @@ def run_reference(args):
     if rank == 0:
         imgs = batch * world * K
         h2d = batch * 784 * 4 + batch * 8
-        print(json.dumps({
+        _emit({
             "metric": "cnn.py images/sec (device-timed, max over ranks)",
             "value": imgs / (ms / 1e3), "unit": "images/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -339,14 +349,14 @@ def run_reference(args):
                     "note": "the reference loop is end to end by construction: synchronous H2D each step, "
                             "loss.item() every 15 steps on rank 0"},
             "gpu_launches": 0,
-        }), flush=True)
+        })
     dist.destroy_process_group()
 
 
 if __name__ == "__main__":
     a = _parse()
     if not torch.cuda.is_available():
-        print(json.dumps({"impl": a.impl, "unavailable": "no CUDA device visible"}))
+        _emit({"impl": a.impl, "unavailable": "no CUDA device visible"})
         sys.exit(0)
     if a.impl == "reference":
         run_reference(a)
