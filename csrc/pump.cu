@@ -1,7 +1,7 @@
 // Native step pump: the per-batch host work of an epoch, done by a C++ loop instead of Python.
 //
 // Replaces the reference's hot loop plumbing (train.py:44-45 DataLoader iteration + .cuda() copies,
-// train.py:55 loss.item()).  Step k of a run uses ring slot k%depth.  Its CUDA graph has two branches:
+// train.py:55 loss.item()).  Step k of a run uses ring slot (base+k)%depth.  Its CUDA graph has two branches:
 // the whole training step (forward, backward, fused reduce+update) on device slot k%depth, and, beside
 // it, the host->device copies of pinned slot (k+1)%depth — the NEXT step's batch — so the upload never
 // sits on the step's critical path.  The step's loss reaches the host without a copy command: the
@@ -37,6 +37,12 @@ struct Pump {
     std::condition_variable cv;
     const int64_t* order = nullptr;
     long req = 0, filled = 0, launched = 0;  // steps to gather / gathered / graphs launched in the current run()
+    // Ring position of the current run's step 0.  A run does not restart at slot 0: it continues behind the slots the
+    // previous run used last (+1 for the slot its last graph pre-fetched into), so that its first batches go into the
+    // slots whose readers finished longest ago — a log-interval boundary then waits for at most one step, not for most
+    // of the queue, before it can gather.
+    long base = 0;
+    int slot_of(long step) const { return (int)((base + step) % d.depth); }
     bool quit = false, busy = false, failed = false;
     int device = 0;
 
@@ -52,7 +58,7 @@ struct Pump {
     bool wquit = false;
 
     void gather_rows(long step, int j0, int j1) {
-        const int s = (int)(step % d.depth);
+        const int s = slot_of(step);
         const int64_t* idx = order + step * (long)d.batch;
         uint8_t* hx = (uint8_t*)d.host_x[s];
         int64_t* hy = (int64_t*)d.host_y[s];
@@ -107,7 +113,7 @@ struct Pump {
             });
             if (quit) return;
             const long k = filled;
-            const int s = (int)(k % d.depth);
+            const int s = slot_of(k);
             busy = true;
             const bool wait_ev = slot_pending[s];
             lk.unlock();
@@ -164,7 +170,7 @@ extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_
     const int inline_steps = n_steps < 2 ? n_steps : 2;
     p->order = order;
     for (int k = 0; k < inline_steps; ++k) {
-        const int sl = k % depth;
+        const int sl = p->slot_of(k);
         bool pend;
         { std::lock_guard<std::mutex> lk(p->mu); pend = p->slot_pending[sl]; }
         if (pend) B200DP_CHECK(cudaEventSynchronize(p->slot_ev[sl]));
@@ -197,18 +203,19 @@ extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_
     // graph of the step before it
     if (!wait_filled(0)) { set_last_error("pump: waiting for a ring slot failed"); rc = (int)cudaErrorUnknown; }
     if (rc == 0) {
-        e = cudaMemcpyAsync(p->d.dev_x[0], p->d.host_x[0], (size_t)p->d.batch * p->d.image_bytes, cudaMemcpyHostToDevice, st);
+        const int s0 = p->slot_of(0);
+        e = cudaMemcpyAsync(p->d.dev_x[s0], p->d.host_x[s0], (size_t)p->d.batch * p->d.image_bytes, cudaMemcpyHostToDevice, st);
         if (e == cudaSuccess)
-            e = cudaMemcpyAsync(p->d.dev_y[0], p->d.host_y[0], (size_t)p->d.batch * sizeof(int64_t), cudaMemcpyHostToDevice, st);
-        if (e == cudaSuccess) e = mark(0);
+            e = cudaMemcpyAsync(p->d.dev_y[s0], p->d.host_y[s0], (size_t)p->d.batch * sizeof(int64_t), cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = mark(s0);
         if (e != cudaSuccess) { set_last_error("pump: first copy: %s", cudaGetErrorString(e)); rc = (int)e; }
     }
     for (long k = 0; rc == 0 && k < n_steps; ++k) {
         if (k + 1 < n_steps && !wait_filled(k + 1)) {          // graph k's prefetch branch reads pinned slot (k+1)%depth
             set_last_error("pump: waiting for a ring slot failed"); rc = (int)cudaErrorUnknown; break;
         }
-        e = cudaGraphLaunch((cudaGraphExec_t)p->d.graph_exec[k % depth], st);
-        if (e == cudaSuccess) e = mark((int)((k + 1) % depth));
+        e = cudaGraphLaunch((cudaGraphExec_t)p->d.graph_exec[p->slot_of(k)], st);
+        if (e == cudaSuccess) e = mark(p->slot_of(k + 1));
         if (e == cudaSuccess && k == 0) { e = cudaEventRecord(p->first_done, st); p->first_valid = true; }
         if (e != cudaSuccess) { set_last_error("pump: step %ld: %s", k, cudaGetErrorString(e)); rc = (int)e; break; }
         {
@@ -221,6 +228,7 @@ extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_
         std::unique_lock<std::mutex> lk(p->mu);
         p->req = 0;                                            // nothing new is started ...
         p->cv.wait(lk, [&] { return !p->busy; });              // ... and a gather in flight (error path) finishes
+        p->base = (p->base + n_steps + 1) % depth;             // next run: behind this run's slots (see Pump::base)
     }
     nvtxRangePop();
     return rc;
