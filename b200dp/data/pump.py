@@ -50,9 +50,7 @@ class StepPump:
         self._graphs = []
         self._handle: Optional[int] = None
         self._loss_keepalive = None
-        self._sink_stage = [torch.zeros(4, dtype=torch.int64).pin_memory() for _ in range(8)]   # in-flight H2D sources
-        self._sink_np = [t.numpy() for t in self._sink_stage]
-        self._sink_i = 0
+        self._sink_ptr = stepper.loss_sink.data_ptr()
 
     # graphs are captured lazily: the stepper wants two eager steps first (lazy module loading)
     def _ensure_graphs(self) -> None:
@@ -120,19 +118,23 @@ class StepPump:
         self._ensure_graphs()
         st._sync_hyper()
         n = n_steps - k0
-        # tell the device where this run's losses go: {array, generation of its element 0, length} — written straight into
-        # a pinned staging vector (one numpy store, one small H2D copy; a ring of vectors because the copies are in flight)
-        stage = self._sink_np[self._sink_i]
+        # the run tells the device where its losses go: {array, generation of its element 0, length} (queued by the C++
+        # side from its own pinned staging ring, ahead of the run's first graph)
+        ring = 0
         if loss_host is not None:
             assert loss_host.dtype == torch.float32 and not loss_host.is_cuda and loss_host.numel() >= n_steps
-            stage[:3] = (loss_host.data_ptr() + 4 * k0, st.optimizer.step_count + 1, n)
-        else:
-            stage[:3] = 0
-        st.loss_sink.copy_(self._sink_stage[self._sink_i], non_blocking=True)
-        self._sink_i = (self._sink_i + 1) % len(self._sink_stage)
+            ring = loss_host.data_ptr() + 4 * k0
+        gen0 = st.optimizer.step_count + 1
         st.optimizer.step_count += n
         self._loss_keepalive = loss_host
-        native.pump_run(self._handle, order[k0 * self.batch:], n)
+        native.pump_run(self._handle, order, n, k0 * self.batch, self._sink_ptr, ring, gen0)
+
+    def pregather(self, order: torch.Tensor, n_steps: int) -> None:
+        """Host-side prefetch across epochs: put the first batches of the NEXT run (sample order ``order``) into their
+        pinned ring slots now, while the GPU works through the steps that are still queued.  The next ``run`` checks the
+        indices and gathers as usual if they differ."""
+        if self._handle is not None and n_steps > 0 and self.stepper._warm >= 2:
+            native.pump_pregather(self._handle, order, n_steps)
 
     def wait_first(self) -> None:
         if self._handle is not None:
@@ -147,5 +149,5 @@ class StepPump:
         if self._handle is not None:
             native.pump_destroy(self._handle)
             self._handle = None
-            self.stepper.loss_sink.zero_()
+            self.stepper.loss_sink[:3].zero_()      # element 3 (the error mirror's address) stays
         self._graphs.clear()

@@ -201,6 +201,15 @@ class PinnedRingLoader:
                 return None
         self._order_ahead = (nxt, _Done, [self._order_for(nxt)])
 
+    def peek_next(self) -> Optional[torch.Tensor]:
+        """The coming epoch's sample order if it has been prepared (``prepare_next`` / the background thread), without
+        consuming it: lets the step pump gather that epoch's first batches ahead of time."""
+        pending = self._order_ahead
+        if pending is None or pending[0] != self.epoch:
+            return None
+        pending[1].join()
+        return pending[2][0]
+
     def _stage(self, slot: int, idx: torch.Tensor) -> int:
         b = idx.numel()
         hx, hy = self._host_x[slot][:b], self._host_y[slot][:b]

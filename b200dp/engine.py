@@ -226,7 +226,12 @@ class Trainer:
             if n_full % self.log_interval == 0 and self.ctx.is_main:
                 last = float(loss.item())
                 self.log.print(train_line(epoch, n_full, len(x), len(loader.dataset), n_batches, last))
-        loader.prepare_next()          # next epoch's sample order, while the GPU works through the queued steps
+        # next epoch's sample order, and its first batches into their pinned ring slots (host-side prefetch, the uploads
+        # stay with their steps), while the GPU works through the queued steps
+        loader.prepare_next()
+        nxt = loader.peek_next()
+        if nxt is not None and not self.dry_run:
+            pump.pregather(nxt, n_full)
         pump.drain()
         self.check_peers()
         return last

@@ -344,7 +344,11 @@ class NativeStepper:
         self._hyper_cache: Optional[Tuple] = None
         self.step_counter = torch.zeros(4, dtype=torch.int32, device=self.device)
         # {mapped pinned loss array, generation at its index 0, its length}: see b200dp_reduce_update
-        self.loss_sink = torch.zeros(4, dtype=torch.int64, device=self.device)
+        # loss_sink[3]: address of a mapped host word; the step's last kernel copies the sticky error word there once it is
+        # set, so that error_flag() is a plain memory read
+        self._err_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self._err_np = self._err_host.numpy()
+        self.loss_sink = torch.tensor([0, 0, 0, self._err_host.data_ptr()], dtype=torch.int64).to(self.device)
         self._graphs: Dict[Tuple[int, int, int], torch.cuda.CUDAGraph] = {}
         self._static_x: Optional[torch.Tensor] = None
         self._static_y: Optional[torch.Tensor] = None
@@ -352,7 +356,6 @@ class NativeStepper:
         self._comm_off = False        # measurement aid: see set_comm_enabled
         self._loss_posted = False
         self._eval_graphs, self._eval_warm = 0, False
-        self._flag_stream, self._flag_host = None, None
         self._pumps = []
         hf = self.net.head_fused
         n = (3 if hf else 5) + (1 if self.net.conv_tc else 0) + (1 if hf else 2) + (3 if self.net.convbwd_tc else 1)
@@ -384,7 +387,7 @@ class NativeStepper:
                              net.partial_stride if is_conv else 0, opt.hyper.code(), self.hyper_dev,
                              self.step_counter, bucket_index == 2,
                              self._comm_struct(b.numel * 4, self.overlap and bucket_index != 2),
-                             net.loss, None if self._loss_posted else self.loss_sink)
+                             None if self._loss_posted else net.loss, self.loss_sink)
 
     def _push(self, bucket_index: int) -> None:
         """Push protocol: send a finished bucket to every peer, wait for nobody."""
@@ -402,8 +405,8 @@ class NativeStepper:
         start, count = (conv.start, conv.numel) if conv_only else (0, self.arena.layout.total)
         native.reduce_update_ll(self.arena.param, self.arena.grad, opt.state0, opt.state1, None, start, count,
                                 net.partials, net.cur_partials, net.partial_stride, conv.start, conv.numel, not pushed,
-                                opt.hyper.code(), self.hyper_dev, self.step_counter, self._comm_struct(0, False), net.loss,
-                                None if self._loss_posted else self.loss_sink, last=True)
+                                opt.hyper.code(), self.hyper_dev, self.step_counter, self._comm_struct(0, False),
+                                None if self._loss_posted else net.loss, self.loss_sink, last=True)
 
     def _dense_update(self, start: int, count: int) -> None:
         """Push protocol, dense buckets (FC.*, conv3: 95 % of the gradient): ONE launch pushes them to every peer, waits
@@ -570,17 +573,13 @@ class NativeStepper:
             self.comm.reset()
 
     def error_flag(self) -> int:
-        """The device's sticky error word, read WITHOUT waiting for the queued steps: a 4-byte copy on a stream of its
-        own (a `.item()` on the compute stream at every log point drained the step pump's queue: one pipeline bubble
-        per log interval, several us per step at short intervals).  The word is sticky, so a value that is one chunk
-        old only delays the report by a log interval."""
-        if self._flag_stream is None:
-            self._flag_stream = torch.cuda.Stream(device=self.device)
-            self._flag_host = torch.zeros(1, dtype=torch.int32).pin_memory()
-        with torch.cuda.stream(self._flag_stream):
-            self._flag_host.copy_(self.step_counter[2:3], non_blocking=True)
-        self._flag_stream.synchronize()
-        return int(self._flag_host[0])
+        """The device's sticky error word, read WITHOUT waiting for the queued steps and without a copy: the last kernel
+        of the step that raised it (and of every later step) stores it into a mapped host word (loss_sink[3]; see
+        ru_finish_step in csrc/opt_math.cuh).  A `.item()` on the compute stream at every log point drained the step
+        pump's queue — one pipeline bubble per log interval — and a 4-byte copy on a stream of its own still cost 30-60 us
+        of host time per check, the last one of an epoch with the GPU idle.  The word is sticky, so a check that runs
+        while the failing step is still in flight only delays the report by a log interval."""
+        return int(self._err_np[0])
 
     def check_error(self) -> None:
         """Raise if a peer did not deliver (synchronises with the compute stream first: for the end of a run / tests)."""

@@ -113,7 +113,8 @@ def load(build_if_missing: bool = True):
     lib.b200dp_symm_close.argtypes = [vp]
     lib.b200dp_fetch_slot.argtypes = [vp, vp, C.c_int64, vp]
     lib.b200dp_pump_create.argtypes = [C.POINTER(vp), C.POINTER(PumpDesc)]
-    lib.b200dp_pump_run.argtypes = [vp, vp, i, vp]
+    lib.b200dp_pump_run.argtypes = [vp, vp, i, vp, C.c_uint64, C.c_uint64, vp]
+    lib.b200dp_pump_pregather.argtypes = [vp, vp, i]
     lib.b200dp_pump_wait_first.argtypes = [vp]
     lib.b200dp_pump_drain.argtypes = [vp]
     lib.b200dp_pump_destroy.argtypes = [vp]
@@ -366,11 +367,21 @@ def pump_create(desc: PumpDesc) -> int:
     return h.value
 
 
-def pump_run(handle: int, order: torch.Tensor, n_steps: int) -> None:
-    """``order``: contiguous CPU int64 sample indices (n_steps*batch of them are read)."""
+def pump_run(handle: int, order: torch.Tensor, n_steps: int, order_offset: int = 0, sink_dev: int = 0,
+             loss_ring_host: int = 0, gen0: int = 0) -> None:
+    """``order``: contiguous CPU int64 sample indices; n_steps*batch of them are read from element ``order_offset`` on.
+    ``sink_dev``: device address of the stepper's loss-sink descriptor (0: leave it alone), ``loss_ring_host``: pinned
+    float32 array that receives the run's losses, ``gen0``: generation of the run's first step."""
     assert order.dtype == torch.int64 and order.is_contiguous() and not order.is_cuda
-    assert order.numel() >= n_steps
-    check(load().b200dp_pump_run(handle, order.data_ptr(), n_steps, _stream()), "pump_run")
+    assert order.numel() - order_offset >= n_steps
+    check(load().b200dp_pump_run(handle, order.data_ptr() + 8 * order_offset, n_steps, sink_dev or None, loss_ring_host,
+                                 gen0, _stream()), "pump_run")
+
+
+def pump_pregather(handle: int, order: torch.Tensor, n_steps: int) -> None:
+    """Gather the first batches of the next run into their ring slots now (see b200dp_pump_pregather)."""
+    assert order.dtype == torch.int64 and order.is_contiguous() and not order.is_cuda
+    check(load().b200dp_pump_pregather(handle, order.data_ptr(), n_steps), "pump_pregather")
 
 
 def pump_wait_first(handle: int) -> None:

@@ -207,9 +207,9 @@ def run_own(args):
     e0.record()
     t0 = time.perf_counter()
     trainer.train_epoch(loader, 1)                          # K steps; returns after the last step finished
+    wall_ms = (time.perf_counter() - t0) * 1e3              # this rank's K steps, losses on the host; max over ranks below
     e1.record()
     _sync_all()
-    wall_ms = (time.perf_counter() - t0) * 1e3
     e2e_ms = _max_ranks(max(e0.elapsed_time(e1), wall_ms), dev)
     stepper.check_error()
     pumped = trainer._pump_for(loader) is not None

@@ -297,7 +297,7 @@ extern "C" int b200dp_reduce_update_ll(float* param, float* grad, float* state0,
     a.partials = partials; a.n_partials = n_partials; a.partial_stride = partial_stride;
     a.p_start = p_start; a.p_count = p_count; a.push_rest = push_rest; a.last = last;
     a.opt_kind = opt_kind; a.hyper = hyper; a.step_counter = step_counter;
-    a.loss_src = loss_src; a.loss_sink = loss_src ? (const unsigned long long*)loss_sink : nullptr;
+    a.loss_src = loss_src; a.loss_sink = (const unsigned long long*)loss_sink;   // sink without src: error mirror only
     if (comm && comm->world > 1) {
         int rc = ll_check_comm(comm, start, count);
         if (rc != 0) return rc;

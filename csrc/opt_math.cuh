@@ -139,11 +139,18 @@ __device__ __forceinline__ void ru_finish_step(uint32_t* step_counter, uint32_t 
         if (atomicAdd(step_counter + 1, 1u) == grid - 1) {
             if (loss_sink != nullptr) {
                 const unsigned long long ring = loss_sink[0], idx = (unsigned long long)gen - loss_sink[1];
-                if (ring != 0ull && idx < loss_sink[2]) {
+                if (loss_src != nullptr && ring != 0ull && idx < loss_sink[2]) {
                     // no system fence: the host reads the slot only after an event that follows this kernel, and a fence
                     // here kept the step's last kernel alive for a PCIe round trip (5 us per step)
                     reinterpret_cast<volatile float*>(ring)[idx] = __ldcg(loss_src);
                 }
+                // loss_sink[3]: mapped host word that receives the sticky error word once it is set, so that the host's
+                // check at a log point is a plain memory read (every CTA that raised the error did so before it took its
+                // ticket).  Nothing is stored while all is well: a store to host memory keeps this kernel alive for a PCIe
+                // round trip.
+                const unsigned long long err_host = loss_sink[3];
+                const uint32_t err = __ldcg(step_counter + 2);
+                if (err_host != 0ull && err != 0u) *reinterpret_cast<volatile uint32_t*>(err_host) = err;
             }
             step_counter[1] = 0u;
             __threadfence();

@@ -13,18 +13,39 @@
 #include <nvtx3/nvToolsExt.h>
 #include <string.h>
 
+#include <stdlib.h>
+#include <time.h>
+
 #include <algorithm>
 #include <atomic>
 #include <condition_variable>
 #include <mutex>
 #include <thread>
+#include <vector>
 
 #include "common.cuh"
 
 namespace b200dp {
 
+// B200DP_PUMP_TRACE=1: host timestamps (CLOCK_MONOTONIC, the clock of Python's time.perf_counter_ns) and device times
+// of every run, printed to stderr by b200dp_pump_drain — where does a short epoch's fixed cost go.
+static inline long now_ns() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (long)ts.tv_sec * 1000000000L + ts.tv_nsec;
+}
+struct RunTrace {
+    static constexpr int kMax = 48;
+    long t_entry = 0, t_inline = 0, t_copy = 0, t_exit = 0, t_launch[kMax] = {}, t_gather0[kMax] = {}, t_gather1[kMax] = {};
+    int n = 0;
+    cudaEvent_t ev_start = nullptr, ev_step[kMax] = {};
+};
+
 struct Pump {
     b200dp_pump_desc d;
+    bool trace = false;
+    std::vector<RunTrace*> runs;
+    RunTrace* cur = nullptr;
     // slot_ev[s]: recorded after the last queued operation that READS pinned slot s (the graph whose prefetch
     // branch copies it to the device, or the explicit copy of a run's first step)
     cudaEvent_t slot_ev[B200DP_PUMP_MAX_DEPTH];
@@ -45,6 +66,20 @@ struct Pump {
     int slot_of(long step) const { return (int)((base + step) % d.depth); }
     bool quit = false, busy = false, failed = false;
     int device = 0;
+    // A run's first batch is uploaded on a stream of its own, beside the steps that are still queued (in the compute
+    // stream the two copies sat between the last graph of one run and the first graph of the next: a ~20 us bubble at
+    // every log-interval boundary).
+    cudaStream_t copy_st = nullptr;
+    cudaEvent_t copy_done = nullptr;
+    // Loss-sink descriptors {array, generation of element 0, length} travel from a small pinned ring (a run's copy may
+    // still be queued when the next run writes its own)
+    static constexpr int kSinkStages = 8;
+    unsigned long long* sink_stage = nullptr;
+    int sink_i = 0;
+    // b200dp_pump_pregather: batches of the NEXT run that already sit in their ring slots, and the sample indices they
+    // were gathered from (the run checks them against its own order)
+    int pre_n = 0;
+    std::vector<int64_t> pre_idx;
 
     // ---- gather: the batch rows are split over a small pool (a 788 KB CIFAR batch gathered row by row by one thread
     // took as long as the GPU step); the helper thread does share 0 and waits for the others ----
@@ -123,7 +158,10 @@ struct Pump {
                 cv.notify_all();
                 continue;
             }
+            RunTrace* tr = cur;
+            if (tr && k < RunTrace::kMax) tr->t_gather0[k] = now_ns();
             gather(k);
+            if (tr && k < RunTrace::kMax) tr->t_gather1[k] = now_ns();
             lk.lock();
             slot_pending[s] = false;
             busy = false;
@@ -147,18 +185,47 @@ extern "C" int b200dp_pump_create(b200dp_pump** out, const b200dp_pump_desc* des
     Pump* p = new Pump();
     p->d = *desc;
     B200DP_CHECK(cudaGetDevice(&p->device));
+    { const char* t = getenv("B200DP_PUMP_TRACE"); p->trace = t && t[0] == '1'; }
     for (int s = 0; s < desc->depth; ++s) {
         B200DP_CHECK(cudaEventCreateWithFlags(&p->slot_ev[s], cudaEventDisableTiming));
         p->slot_pending[s] = false;
     }
     B200DP_CHECK(cudaEventCreateWithFlags(&p->first_done, cudaEventDisableTiming));
+    B200DP_CHECK(cudaStreamCreateWithFlags(&p->copy_st, cudaStreamNonBlocking));
+    B200DP_CHECK(cudaEventCreateWithFlags(&p->copy_done, cudaEventDisableTiming));
+    B200DP_CHECK(cudaHostAlloc((void**)&p->sink_stage, Pump::kSinkStages * 4 * sizeof(unsigned long long), cudaHostAllocDefault));
     for (int w = 0; w < Pump::kWorkers; ++w) p->workers[w] = std::thread([p, w] { p->worker_main(w); });
     p->helper = std::thread([p] { p->helper_main(); });
     *out = (b200dp_pump*)p;
     return 0;
 }
 
-extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_steps, b200dp_stream_t stream) {
+// Gather the first batches of the NEXT run into their ring slots now (call it while the GPU still works through the
+// previous run): the next b200dp_pump_run with the same leading sample indices starts with its upload instead of ~15 us
+// of gathering per batch with the GPU idle.  Host work only; the upload stays with the run.
+extern "C" int b200dp_pump_pregather(b200dp_pump* handle, const int64_t* order, int n_steps) {
+    Pump* p = (Pump*)handle;
+    B200DP_REQUIRE(p && order && n_steps >= 0, "bad arguments");
+    const int n = n_steps < 2 ? n_steps : 2;
+    p->pre_n = 0;
+    p->order = order;
+    for (int k = 0; k < n; ++k) {
+        const int sl = p->slot_of(k);
+        bool pend;
+        { std::lock_guard<std::mutex> lk(p->mu); pend = p->slot_pending[sl]; }
+        if (pend) B200DP_CHECK(cudaEventSynchronize(p->slot_ev[sl]));
+        p->gather(k);
+        std::lock_guard<std::mutex> lk(p->mu);
+        p->slot_pending[sl] = false;
+    }
+    p->pre_idx.assign(order, order + (size_t)n * p->d.batch);
+    p->pre_n = n;
+    p->order = nullptr;
+    return 0;
+}
+
+extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_steps, uint64_t* sink_dev,
+                               uint64_t loss_ring_host, uint64_t gen0, b200dp_stream_t stream) {
     Pump* p = (Pump*)handle;
     B200DP_REQUIRE(p && order && n_steps >= 0, "bad arguments");
     if (n_steps == 0) return 0;
@@ -169,7 +236,28 @@ extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_
     // thread wake-ups (~30-50 us each) with the GPU idle at the start of every epoch / log interval.
     const int inline_steps = n_steps < 2 ? n_steps : 2;
     p->order = order;
-    for (int k = 0; k < inline_steps; ++k) {
+    RunTrace* tr = nullptr;
+    if (p->trace) {
+        tr = new RunTrace();
+        tr->n = std::min(n_steps, (int)RunTrace::kMax);
+        B200DP_CHECK(cudaEventCreate(&tr->ev_start));
+        for (int k = 0; k < tr->n; ++k) B200DP_CHECK(cudaEventCreate(&tr->ev_step[k]));
+        tr->t_entry = now_ns();
+        B200DP_CHECK(cudaEventRecord(tr->ev_start, st));
+        std::lock_guard<std::mutex> lk(p->mu);
+        p->cur = tr;
+        p->runs.push_back(tr);
+    }
+    int pre = std::min(p->pre_n, inline_steps);       // batches that b200dp_pump_pregather has put in place already
+    if (pre > 0 && memcmp(order, p->pre_idx.data(), (size_t)pre * p->d.batch * sizeof(int64_t)) != 0) pre = 0;
+    p->pre_n = 0;
+    if (sink_dev != nullptr) {     // where this run's losses go: queued before the run's first graph
+        unsigned long long* stg = p->sink_stage + 4 * p->sink_i;
+        p->sink_i = (p->sink_i + 1) % Pump::kSinkStages;
+        stg[0] = loss_ring_host; stg[1] = gen0; stg[2] = loss_ring_host ? (unsigned long long)n_steps : 0ull;
+        B200DP_CHECK(cudaMemcpyAsync(sink_dev, stg, 3 * sizeof(unsigned long long), cudaMemcpyHostToDevice, st));
+    }
+    for (int k = pre; k < inline_steps; ++k) {
         const int sl = p->slot_of(k);
         bool pend;
         { std::lock_guard<std::mutex> lk(p->mu); pend = p->slot_pending[sl]; }
@@ -178,6 +266,7 @@ extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_
         std::lock_guard<std::mutex> lk(p->mu);
         p->slot_pending[sl] = false;
     }
+    if (tr) tr->t_inline = now_ns();
     {
         std::lock_guard<std::mutex> lk(p->mu);
         p->req = n_steps;
@@ -203,12 +292,26 @@ extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_
     // graph of the step before it
     if (!wait_filled(0)) { set_last_error("pump: waiting for a ring slot failed"); rc = (int)cudaErrorUnknown; }
     if (rc == 0) {
-        const int s0 = p->slot_of(0);
-        e = cudaMemcpyAsync(p->d.dev_x[s0], p->d.host_x[s0], (size_t)p->d.batch * p->d.image_bytes, cudaMemcpyHostToDevice, st);
-        if (e == cudaSuccess)
-            e = cudaMemcpyAsync(p->d.dev_y[s0], p->d.host_y[s0], (size_t)p->d.batch * sizeof(int64_t), cudaMemcpyHostToDevice, st);
+        const int s0 = p->slot_of(0), s1 = (s0 + 1) % depth;
+        // Device slot s0 is free once the last graph that read it has finished; that graph recorded slot_ev[s1] (every
+        // graph marks the slot after its own), and the last writer of the slot (a prefetch branch) recorded slot_ev[s0],
+        // which the gather above has waited for.  An event that was never recorded does not block.
+        e = cudaStreamWaitEvent(p->copy_st, p->slot_ev[s1], 0);
+        const size_t xb = (size_t)p->d.batch * p->d.image_bytes, yb = (size_t)p->d.batch * sizeof(int64_t);
+        const ptrdiff_t hoff = (const char*)p->d.host_y[s0] - (const char*)p->d.host_x[s0];
+        const ptrdiff_t doff = (const char*)p->d.dev_y[s0] - (const char*)p->d.dev_x[s0];
+        if (e == cudaSuccess && hoff == doff && hoff >= (ptrdiff_t)xb && hoff < (ptrdiff_t)xb + 64) {
+            // images and labels share one allocation on both sides: one copy
+            e = cudaMemcpyAsync(p->d.dev_x[s0], p->d.host_x[s0], (size_t)hoff + yb, cudaMemcpyHostToDevice, p->copy_st);
+        } else if (e == cudaSuccess) {
+            e = cudaMemcpyAsync(p->d.dev_x[s0], p->d.host_x[s0], xb, cudaMemcpyHostToDevice, p->copy_st);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(p->d.dev_y[s0], p->d.host_y[s0], yb, cudaMemcpyHostToDevice, p->copy_st);
+        }
+        if (e == cudaSuccess) e = cudaEventRecord(p->copy_done, p->copy_st);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(st, p->copy_done, 0);
         if (e == cudaSuccess) e = mark(s0);
         if (e != cudaSuccess) { set_last_error("pump: first copy: %s", cudaGetErrorString(e)); rc = (int)e; }
+        if (tr) tr->t_copy = now_ns();
     }
     for (long k = 0; rc == 0 && k < n_steps; ++k) {
         if (k + 1 < n_steps && !wait_filled(k + 1)) {          // graph k's prefetch branch reads pinned slot (k+1)%depth
@@ -217,6 +320,7 @@ extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_
         e = cudaGraphLaunch((cudaGraphExec_t)p->d.graph_exec[p->slot_of(k)], st);
         if (e == cudaSuccess) e = mark(p->slot_of(k + 1));
         if (e == cudaSuccess && k == 0) { e = cudaEventRecord(p->first_done, st); p->first_valid = true; }
+        if (tr && k < tr->n) { tr->t_launch[k] = now_ns(); if (e == cudaSuccess) e = cudaEventRecord(tr->ev_step[k], st); }
         if (e != cudaSuccess) { set_last_error("pump: step %ld: %s", k, cudaGetErrorString(e)); rc = (int)e; break; }
         {
             std::lock_guard<std::mutex> lk(p->mu);
@@ -229,7 +333,9 @@ extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_
         p->req = 0;                                            // nothing new is started ...
         p->cv.wait(lk, [&] { return !p->busy; });              // ... and a gather in flight (error path) finishes
         p->base = (p->base + n_steps + 1) % depth;             // next run: behind this run's slots (see Pump::base)
+        p->cur = nullptr;
     }
+    if (tr) tr->t_exit = now_ns();
     nvtxRangePop();
     return rc;
 }
@@ -245,6 +351,27 @@ extern "C" int b200dp_pump_drain(b200dp_pump* handle) {
             std::lock_guard<std::mutex> lk(p->mu);
             p->slot_pending[s] = false;
         }
+    }
+    if (p->trace && !p->runs.empty()) {
+        const long t_drained = now_ns();
+        B200DP_CHECK(cudaDeviceSynchronize());
+        for (RunTrace* tr : p->runs) {
+            const long t0 = tr->t_entry;
+            fprintf(stderr, "[pump trace] run of %d steps: entry %ld ns | inline gathers done +%.1f us | first copy queued +%.1f | "
+                    "returned +%.1f | drained +%.1f\n", tr->n, t0, (tr->t_inline - t0) / 1e3, (tr->t_copy - t0) / 1e3,
+                    (tr->t_exit - t0) / 1e3, (t_drained - t0) / 1e3);
+            for (int k = 0; k < tr->n; ++k) {
+                float ms = 0.f;
+                cudaEventElapsedTime(&ms, tr->ev_start, tr->ev_step[k]);
+                fprintf(stderr, "[pump trace]   step %2d: gathered %+8.1f..%+8.1f us  launched %+8.1f us  finished on the device %+8.1f us\n",
+                        k, tr->t_gather0[k] ? (tr->t_gather0[k] - t0) / 1e3 : 0.0, tr->t_gather1[k] ? (tr->t_gather1[k] - t0) / 1e3 : 0.0,
+                        (tr->t_launch[k] - t0) / 1e3, ms * 1e3);
+                cudaEventDestroy(tr->ev_step[k]);
+            }
+            cudaEventDestroy(tr->ev_start);
+            delete tr;
+        }
+        p->runs.clear();
     }
     return 0;
 }
@@ -277,6 +404,9 @@ extern "C" int b200dp_pump_destroy(b200dp_pump* handle) {
         cudaEventDestroy(p->slot_ev[s]);
     }
     cudaEventDestroy(p->first_done);
+    cudaEventDestroy(p->copy_done);
+    cudaStreamDestroy(p->copy_st);
+    cudaFreeHost(p->sink_stage);
     delete p;
     return 0;
 }

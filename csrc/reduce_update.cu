@@ -301,7 +301,7 @@ extern "C" int b200dp_reduce_update(float* param, float* grad, float* state0, fl
     a.start = start; a.count = count;
     a.partials = partials; a.n_partials = n_partials; a.partial_stride = partial_stride;
     a.opt_kind = opt_kind; a.hyper = hyper; a.step_counter = step_counter; a.last_bucket = last_bucket;
-    a.loss_src = loss_src; a.loss_sink = (loss_src && last_bucket) ? (const unsigned long long*)loss_sink : nullptr;
+    a.loss_src = loss_src; a.loss_sink = last_bucket ? (const unsigned long long*)loss_sink : nullptr;
     if (comm) {
         a.comm = *comm;
         B200DP_REQUIRE(comm->world >= 1 && comm->world <= 8, "world size 1..8");

@@ -230,9 +230,11 @@ int b200dp_conv_bwd_noalloc(const void* x, int in_is_u8, float mean, float std, 
  * bucket kept CTA 0 waiting for the peers' lines — the exposed part of the exchange.  The LAST
  * bucket launch of a step (last_bucket != 0) advances the generation.
  * loss_src / loss_sink (both nullable; used by the last bucket launch only): loss_sink is a device
- * uint64[3] = {address of a mapped pinned float array (0 = off), generation stored at index 0,
- * array length}; the step with generation g stores *loss_src into array[g - sink[1]] — how the
- * loss reaches the host without a copy command (train.py:55 loss.item()). */
+ * uint64[4] = {address of a mapped pinned float array (0 = off), generation stored at index 0,
+ * array length, address of a mapped pinned uint32 (0 = off)}; the step with generation g stores *loss_src
+ * (when loss_src is given) into array[g - sink[1]] — how the loss reaches the host without a copy command
+ * (train.py:55 loss.item()) — and, once the error word step_counter[2] is set, copies it to the uint32: the
+ * host's check for a dead peer is then a plain memory read. */
 typedef struct {
     int world, rank;
     int algo;                 /* 0 one-shot: every rank reads every peer's slice (latency regime);
@@ -294,7 +296,7 @@ int b200dp_reduce_update_ll(float* param, float* grad, float* state0, float* sta
 /* The step's loss to the host without a copy command and off the step's dependency chain: a one-thread kernel stores
  * *loss_src into the mapped pinned array described by loss_sink (slot = step_counter[0] + 1 - sink[1]; see
  * b200dp_reduce_update).  Launch it on a stream beside the backward pass, after the kernel that produced the loss and
- * before the step's last reduce+update launch (which advances step_counter[0]); pass that launch loss_sink = NULL.
+ * before the step's last reduce+update launch (which advances step_counter[0]); pass that launch loss_src = NULL.
  * (A kernel that stores to host memory stays alive for a PCIe round trip; inside the last kernel of the step that was
  * 5 us per step.)  Replaces train.py:55 loss.item(). */
 int b200dp_post_loss(const float* loss_src, const uint32_t* step_counter, const uint64_t* loss_sink, b200dp_stream_t s);
@@ -340,7 +342,14 @@ typedef struct {
  * nothing on the step's critical path, a memcpy node cost ~4 us per step.  Replaces train.py:45 (.cuda() copies). */
 int b200dp_fetch_slot(void* dst_device, const void* src_pinned_host, int64_t bytes, b200dp_stream_t s);
 int b200dp_pump_create(b200dp_pump** out, const b200dp_pump_desc* desc);
-int b200dp_pump_run(b200dp_pump* p, const int64_t* order, int n_steps, b200dp_stream_t s);
+/* sink_dev (nullable): the stepper's loss-sink descriptor on the device; the run points it at loss_ring_host (a mapped
+ * pinned float array, element k = loss of the run's step k; 0 = off), gen0 = generation of the run's first step. */
+int b200dp_pump_run(b200dp_pump* p, const int64_t* order, int n_steps, uint64_t* sink_dev, uint64_t loss_ring_host,
+                    uint64_t gen0, b200dp_stream_t s);
+/* Host-side prefetch across runs: gather the first (two) batches of the NEXT run into their ring slots now, while the
+ * GPU works through the queued steps.  The next b200dp_pump_run uses them if its order starts with the same sample
+ * indices, and gathers as usual otherwise.  The upload stays inside the run. */
+int b200dp_pump_pregather(b200dp_pump* p, const int64_t* order, int n_steps);
 int b200dp_pump_wait_first(b200dp_pump* p);   /* until step 0 of the latest run finished */
 int b200dp_pump_drain(b200dp_pump* p);
 int b200dp_pump_destroy(b200dp_pump* p);
