@@ -118,8 +118,8 @@ class StepPump:
         self._ensure_graphs()
         st._sync_hyper()
         n = n_steps - k0
-        # the run tells the device where its losses go: {array, generation of its element 0, length} (queued by the C++
-        # side from its own pinned staging ring, ahead of the run's first graph)
+        # the run tells the device where its losses go: {array, generation of its element 0, length} (a one-thread kernel
+        # queued by the C++ side ahead of the run's first graph)
         ring = 0
         if loss_host is not None:
             assert loss_host.dtype == torch.float32 and not loss_host.is_cuda and loss_host.numel() >= n_steps

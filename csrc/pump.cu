@@ -71,11 +71,6 @@ struct Pump {
     // every log-interval boundary).
     cudaStream_t copy_st = nullptr;
     cudaEvent_t copy_done = nullptr;
-    // Loss-sink descriptors {array, generation of element 0, length} travel from a small pinned ring (a run's copy may
-    // still be queued when the next run writes its own)
-    static constexpr int kSinkStages = 8;
-    unsigned long long* sink_stage = nullptr;
-    int sink_i = 0;
     // b200dp_pump_pregather: batches of the NEXT run that already sit in their ring slots, and the sample indices they
     // were gathered from (the run checks them against its own order)
     int pre_n = 0;
@@ -175,6 +170,11 @@ struct Pump {
 
 using namespace b200dp;
 
+__global__ void set_sink_kernel(unsigned long long* sink, unsigned long long ring, unsigned long long gen0,
+                                unsigned long long len) {
+    sink[0] = ring; sink[1] = gen0; sink[2] = len;
+}
+
 extern "C" int b200dp_pump_create(b200dp_pump** out, const b200dp_pump_desc* desc) {
     B200DP_REQUIRE(out && desc, "null argument");
     B200DP_REQUIRE(desc->depth >= 2 && desc->depth <= B200DP_PUMP_MAX_DEPTH, "depth 2..8");
@@ -193,7 +193,6 @@ extern "C" int b200dp_pump_create(b200dp_pump** out, const b200dp_pump_desc* des
     B200DP_CHECK(cudaEventCreateWithFlags(&p->first_done, cudaEventDisableTiming));
     B200DP_CHECK(cudaStreamCreateWithFlags(&p->copy_st, cudaStreamNonBlocking));
     B200DP_CHECK(cudaEventCreateWithFlags(&p->copy_done, cudaEventDisableTiming));
-    B200DP_CHECK(cudaHostAlloc((void**)&p->sink_stage, Pump::kSinkStages * 4 * sizeof(unsigned long long), cudaHostAllocDefault));
     for (int w = 0; w < Pump::kWorkers; ++w) p->workers[w] = std::thread([p, w] { p->worker_main(w); });
     p->helper = std::thread([p] { p->helper_main(); });
     *out = (b200dp_pump*)p;
@@ -251,11 +250,13 @@ extern "C" int b200dp_pump_run(b200dp_pump* handle, const int64_t* order, int n_
     int pre = std::min(p->pre_n, inline_steps);       // batches that b200dp_pump_pregather has put in place already
     if (pre > 0 && memcmp(order, p->pre_idx.data(), (size_t)pre * p->d.batch * sizeof(int64_t)) != 0) pre = 0;
     p->pre_n = 0;
-    if (sink_dev != nullptr) {     // where this run's losses go: queued before the run's first graph
-        unsigned long long* stg = p->sink_stage + 4 * p->sink_i;
-        p->sink_i = (p->sink_i + 1) % Pump::kSinkStages;
-        stg[0] = loss_ring_host; stg[1] = gen0; stg[2] = loss_ring_host ? (unsigned long long)n_steps : 0ull;
-        B200DP_CHECK(cudaMemcpyAsync(sink_dev, stg, 3 * sizeof(unsigned long long), cudaMemcpyHostToDevice, st));
+    if (sink_dev != nullptr) {
+        // where this run's losses go: a one-thread kernel with the three words as arguments, queued behind the previous
+        // run's last graph (whose steps still use the old descriptor) and ahead of this run's first (a 24-byte copy here
+        // is a copy-engine command between two graphs: ~5 us of bubble per run)
+        set_sink_kernel<<<1, 1, 0, st>>>((unsigned long long*)sink_dev, loss_ring_host, gen0,
+                                         loss_ring_host ? (unsigned long long)n_steps : 0ull);
+        B200DP_CHECK(cudaGetLastError());
     }
     for (int k = pre; k < inline_steps; ++k) {
         const int sl = p->slot_of(k);
@@ -406,7 +407,6 @@ extern "C" int b200dp_pump_destroy(b200dp_pump* handle) {
     cudaEventDestroy(p->first_done);
     cudaEventDestroy(p->copy_done);
     cudaStreamDestroy(p->copy_st);
-    cudaFreeHost(p->sink_stage);
     delete p;
     return 0;
 }

@@ -78,3 +78,43 @@ def test_pump_direct_api_losses():
     assert [float(v) for v in losses] == ref
     assert b.optimizer.step_count == 10 and int(b.step_counter[0]) == 10
     a.close(); b.close()
+
+
+def test_pump_pregather_hit_and_miss():
+    """StepPump.pregather puts the next run's first batches into their ring slots ahead of time.  A run whose order starts
+    with the same indices uses them; a run with another order must notice and gather its own — in both cases the
+    parameters and losses equal the step-by-step path."""
+    from b200dp.data.synthetic import MNIST_SPEC, SyntheticImages
+    from b200dp.models.fused import NativeStepper
+    from b200dp.optim.flat import OptHyper
+    from b200dp.parallel.launch import RankContext
+    dev = torch.device("cuda", 0)
+    ctx = RankContext(0, 1, 0, dev, "nccl")
+    B, n = 32, 16
+    base = SyntheticImages(B * n, MNIST_SPEC, seed=9)
+    g = torch.Generator().manual_seed(2)
+    orders = [torch.randperm(B * n, generator=g) for _ in range(3)]       # three "epochs" of 16, 5 and 5 steps
+    steps = [n, 5, 5]
+
+    def make():
+        torch.manual_seed(7)
+        return NativeStepper(ctx, MNIST_LENET, OptHyper("sgd", lr=0.05), batch=B, loss_mode="xent", graph=True,
+                             dtype="fp32")
+    a = make()
+    ref = []
+    for order, k_n in zip(orders, steps):
+        for k in range(k_n):
+            idx = order[k * B:(k + 1) * B]
+            ref.append(float(a.train_step(base.images[idx].to(dev), base.targets[idx].to(dev))))
+    b = make()
+    pump = b.make_pump(base.images, base.targets, B)
+    losses = torch.full((sum(steps),), float("nan")).pin_memory()
+    pump.run(orders[0], steps[0], losses)
+    pump.pregather(orders[1], steps[1])               # hit: the next run starts with these batches
+    pump.run(orders[1], steps[1], losses[steps[0]:])
+    pump.pregather(orders[0], steps[2])               # miss: prepared for another order than the one that runs
+    pump.run(orders[2], steps[2], losses[steps[0] + steps[1]:])
+    pump.drain()
+    assert [float(v) for v in losses] == ref
+    assert torch.equal(a.arena.param, b.arena.param)
+    a.close(); b.close()

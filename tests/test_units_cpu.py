@@ -197,6 +197,8 @@ def test_loader_prepares_next_epoch_order():
     mk = lambda: PinnedRingLoader(ds.images, ds.targets, 10, 290, 32, MNIST_SPEC, fmt="f32", seed=4)   # noqa: E731
     a, b = mk(), mk()
     for _ in range(3):
+        assert b.peek_next() is None                           # nothing prepared on the on-demand loader
         oa = a._order(); a.epoch += 1; a.prepare_next()        # what the pumped training loop does
         ob = b._order_for(b.epoch); b.epoch += 1               # on demand
         assert torch.equal(oa, ob) and sorted(oa.tolist()) == list(range(10, 290))
+        assert torch.equal(a.peek_next(), a._order_for(a.epoch))    # the coming epoch's order, not consumed by the peek
