@@ -167,6 +167,10 @@ int b200dp_tcw_conv_wgrad(int layer, const void* x, int in_is_u8, float mean, fl
 /* Profiling aid: while dbg != NULL, CTA 0 of every window-tile launch writes clock64() stamps of its phases
  * (start, set-up, staged, barrier, MMAs issued, accumulators ready, epilogue done, end) to dbg[0..8). */
 void b200dp_tcw_set_debug(long long* dbg);
+/* Same for the weight-gradient kernels (stamps: start, set-up, planes of image 0, dZ of image 0, chunk 0 / 1 staged,
+ * MMAs done, end; bench/wg_probe.py) and for the tf32 GEMM (pipeline stamps; bench/tc_probe.py). */
+void b200dp_tcw_wgrad_set_debug(long long* dbg);
+void b200dp_tc_gemm_set_debug(long long* dbg);
 
 /* Fused convolution backward for one step: pool2-bwd + leaky-bwd + conv2 dgrad
  * + conv2 wgrad/bgrad + pool1-bwd + leaky-bwd + conv1 wgrad/bgrad (no conv1

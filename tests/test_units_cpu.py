@@ -171,6 +171,15 @@ def test_native_library_builds_for_sm100a():
     assert len(names) > 30
     missing = [n for n in sorted(names) if not hasattr(h, n)]
     assert not missing, missing
+    # and the other way round: every entry point the sources define, and every one the ctypes layer binds, is declared
+    root = os.path.join(os.path.dirname(os.path.dirname(lib)), "..")
+    import glob
+    defined = set()
+    for f in glob.glob(os.path.join(root, "csrc", "*.cu")):
+        defined |= set(re.findall(r'extern "C"[^;{(]*?\b(b200dp_[a-z0-9_]+)\s*\(', open(f).read()))
+    assert len(defined) > 30 and not sorted(defined - names), sorted(defined - names)
+    bound = set(re.findall(r"\blib\.(b200dp_[a-z0-9_]+)\.", open(os.path.join(root, "b200dp", "ops", "native.py")).read()))
+    assert len(bound) > 20 and not sorted(bound - names), sorted(bound - names)
 
 
 def test_push_threshold_and_new_cli_flags():
