@@ -65,6 +65,8 @@ def build_parser() -> argparse.ArgumentParser:
                         "the rest on tcgen05); auto = measured-fastest for the model")
     p.add_argument("--peer-timeout-ms", type=int, default=0,
                    help="bound on every wait for a peer rank's gradients (0 = 20 s); a rank that does not deliver raises")
+    p.add_argument("--pin-cores", action="store_true",
+                   help="pin every rank's host threads (Python, step pump) to a disjoint slice of the node's CPU cores")
     p.add_argument("--no-overlap", action="store_true", help="reduce after backward, not during it")
     p.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
     p.add_argument("--no-pump", action="store_true",

@@ -332,6 +332,13 @@ def load_datasets(args, spec):
 
 def run(ctx: RankContext, args) -> dict:
     """Per-rank entry (reference ``run(rank, size, args)``, train.py:79-108)."""
+    if getattr(args, "pin_cores", False) and ctx.world_size > 1:
+        from .parallel.launch import pin_to_core_share
+        n_local = int(__import__("os").environ.get("LOCAL_WORLD_SIZE", ctx.world_size))
+        share = pin_to_core_share(ctx.local_rank % max(n_local, 1), n_local)
+        if ctx.is_main:
+            print(f"host threads pinned: rank 0 runs on cores {sorted(share)}" if share else
+                  "host threads not pinned (fewer than two cores per rank)")
     torch.manual_seed(args.seed)                      # train.py:80 — same seed on every rank
     if ctx.device.type == "cuda":
         torch.cuda.manual_seed(args.seed)             # train.py:81

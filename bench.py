@@ -62,6 +62,7 @@ def _parse():
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--no-overlap", action="store_true")
     p.add_argument("--no-pump", action="store_true", help="e2e: drive every step from Python")
+    p.add_argument("--pin-cores", action="store_true", help="pin each rank's host threads to its own slice of the cores")
     p.add_argument("--conv", choices=["auto", "simt", "tc", "hybrid"], default="auto",
                    help="convolution kernels: CUDA-core fp32, window-tile tcgen05 (bf16 operands), or hybrid = first layer "
                         "on CUDA cores + everything after it on tcgen05 (auto: measured-fastest for the model)")
@@ -139,6 +140,9 @@ def run_own(args):
     from b200dp.utils.clocks import ClockSampler
 
     rank, world, local, dev = _init_dist(args.gpus)
+    if args.pin_cores and world > 1:
+        from b200dp.parallel.launch import pin_to_core_share
+        pin_to_core_share(local, int(os.environ.get("LOCAL_WORLD_SIZE", world)))
     cfg, spec = _model_cfg(args.config)
     batch = PER_GPU_BATCH if args.config != "strong4096" else math.ceil(4096 / world)
     ctx = RankContext(rank, world, local, dev, "nccl")

@@ -211,3 +211,17 @@ def test_loader_prepares_next_epoch_order():
         ob = b._order_for(b.epoch); b.epoch += 1               # on demand
         assert torch.equal(oa, ob) and sorted(oa.tolist()) == list(range(10, 290))
         assert torch.equal(a.peek_next(), a._order_for(a.epoch))    # the coming epoch's order, not consumed by the peek
+
+
+def test_core_shares_are_disjoint_and_cover_whole_slices():
+    """--pin-cores: every rank of a node gets its own contiguous slice of the allowed cores; too few cores: no pinning."""
+    from b200dp.cli import parse_args
+    from b200dp.parallel.launch import core_share
+    allowed = set(range(4, 36))                         # 32 cores, not starting at 0
+    shares = [core_share(r, 8, allowed) for r in range(8)]
+    assert all(len(s) == 4 for s in shares)
+    assert set().union(*shares) == allowed and sum(len(s) for s in shares) == 32
+    assert shares[0] == {4, 5, 6, 7} and shares[7] == {32, 33, 34, 35}
+    assert core_share(0, 8, set(range(8))) is None      # one core per rank
+    assert core_share(1, 3, set(range(8))) == {2, 3}    # the remainder stays unused
+    assert parse_args(["--pin-cores"]).pin_cores and not parse_args([]).pin_cores
